@@ -1,0 +1,159 @@
+/*
+ * rtp.h - C ABI of the B200-native ray-tracing hot path (libflyscene_b200.so).
+ *
+ * This is the drop-in boundary for plindhorst/Ray-Tracing-Project's one data-parallel path:
+ * Flyscene::raytraceScene / traceRayThread / traceRay and everything under them
+ * (reference src/flyscene.cpp:250-614, src/BoundingBox.cpp:7-161).  The reference has no
+ * FFI of its own - its boundary is the Flyscene / BoundingBox C++ class surface - so each
+ * entry point below names the reference member it replaces.  The C++ mirror classes in
+ * ray-tracing-project_b200/host/ (Flyscene, BoundingBox, Flycamera) are thin callers of this
+ * ABI; INTEGRATION.md shows the binding a reference maintainer would add.
+ *
+ * Conventions: plain pointers and sizes, caller owns all host buffers, the library owns all
+ * device memory behind the opaque rtp_scene handle.  Every function returns 0 on success and
+ * a negative rtp_status on failure; rtp_last_error() gives the message (thread-local).  No
+ * exceptions cross the ABI.  There is NO CPU fallback: without a CUDA device every compute
+ * entry point fails with RTP_ERR_CUDA.
+ */
+#ifndef RTP_H
+#define RTP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTP_ABI_VERSION 1
+
+typedef enum rtp_status {
+  RTP_OK = 0,
+  RTP_ERR_INVALID = -1, /* bad argument                                   */
+  RTP_ERR_CUDA = -2,    /* CUDA runtime error or no device                */
+  RTP_ERR_NOMEM = -3,
+  RTP_ERR_STATE = -4    /* call order (e.g. render before set_camera)     */
+} rtp_status;
+
+typedef struct rtp_scene rtp_scene; /* opaque */
+
+/* The mesh exactly as the reference's Tucano::Mesh holds it after loadObjFile +
+ * normalizeModelMatrix (flyscene.cpp:18-22; tucano/mesh.hpp:238-248,387,395,426).
+ * Object space; the library flattens it once into world-space SoA float4 + a linear BVH. */
+typedef struct rtp_mesh {
+  int32_t n_verts, n_faces, n_mats, n_boxes;
+  const float *verts;       /* V x 4  Mesh::getVertex(i), w = 1                          */
+  const float *normals;     /* V x 3  Mesh::getNormal(i) (not necessarily unit)          */
+  const int32_t *faces;     /* F x 3  Face::vertex_ids                                   */
+  const int32_t *face_mat;  /* F      Face::material_id (-1 = none)                      */
+  const float *face_normal; /* F x 3  Face::normal, or NULL: built as mesh.hpp:475-477   */
+  const float *materials;   /* M x 12 per Mtl: ka[3] kd[3] ks[3] Ns Ni d (mtl.hpp:17-37) */
+  float shape[12];          /* Model::getShapeModelMatrix(), 3x4 row-major (model.hpp:102) */
+  /* The BoundingBox list in creation order (BoundingBox.h:13,16,17,26).  It fixes which faces
+   * a ray may see (flyscene.cpp:381-393) and the first-visited-wins tie order.  n_boxes = 0
+   * with NULL pointers: the library builds it with the reference's splitter
+   * (flyscene.cpp:399-418) using min_faces / max_boxes below. */
+  const float *boxes;         /* B x 6: low[3] high[3], object space */
+  const int32_t *box_off;     /* B + 1 */
+  const int32_t *box_faces;   /* F face ids in box order */
+  int32_t min_faces;          /* Flyscene::MIN_FACES (300) when 0 */
+  int32_t max_boxes;          /* Flyscene::MAX_BOXES (INT_MAX) when 0 */
+} rtp_mesh;
+
+/* Tucano::Camera state read by screenToWorld / getCenter (camera.hpp:115-118,155-173). */
+typedef struct rtp_camera {
+  float view[12];    /* Camera::view_matrix, 3x4 row-major                */
+  float viewport[4]; /* Camera::viewport (x, y, w, h)                     */
+  float fovy;        /* degrees, as given to setPerspectiveMatrix         */
+  float aspect;      /* aspect_ratio as given to setPerspectiveMatrix     */
+} rtp_camera;
+
+/* Flyscene::lights / Flyscene::dirLights (flyscene.hpp:132,135): 6 floats each,
+ * position-or-vector[3] then rgb[3].  Directional vectors are used verbatim, unnormalised
+ * (flyscene.cpp:611). */
+typedef struct rtp_lights {
+  int32_t n_point, n_dir;
+  const float *point;
+  const float *dir;
+} rtp_lights;
+
+typedef struct rtp_render_opts {
+  int32_t width, height; /* image size; the camera's viewport drives ray generation       */
+  int32_t max_depth;     /* Flyscene::max_depth (2): reflection depth D <=> max_depth D+1  */
+  float background[3];   /* Flyscene::BACKGROUND_COLOR                                    */
+  int32_t rank, world;   /* tile sharding: this process renders tiles with owner == rank   */
+  int32_t flags;         /* RTP_RENDER_* */
+} rtp_render_opts;
+#define RTP_RENDER_DEFAULT 0
+
+typedef struct rtp_stats {
+  int64_t rays_primary, rays_shadow, rays_reflection, hits;
+  float ms_trace;       /* device time of the traced region (CUDA events)                  */
+  float ms_total;       /* device time incl. output conversion, excl. H2D/D2H              */
+  int32_t kernel_launches;
+  int32_t n_bvh_nodes, n_triangles;
+  float ms_closest, ms_anyhit; /* summed device time of the two traversal kernels           */
+} rtp_stats;
+
+/* ---- lifetime ---------------------------------------------------------------------------- */
+/* Replaces Flyscene::initialize's scene side + generateBoundingBoxes (flyscene.cpp:18-22,62,
+ * 399-428).  device = CUDA ordinal (-1: current). */
+int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out);
+int rtp_scene_destroy(rtp_scene *s); /* ~Flyscene / BoundingBox::deconstruct */
+
+/* Flyscene::lights, dirLights (public members, flyscene.hpp:132,135). */
+int rtp_set_lights(rtp_scene *s, const rtp_lights *l);
+/* getCamera()->setViewport / setPerspectiveMatrix / view matrix (flyscene.cpp:14-15). */
+int rtp_set_camera(rtp_scene *s, const rtp_camera *c);
+
+/* ---- the render entry point --------------------------------------------------------------- */
+/* Replaces Flyscene::raytraceScene + traceRayThread (flyscene.cpp:250-314) for the full
+ * W x H frame.  Host outputs, each optional (NULL to skip):
+ *   rgb   W*H*3 float  pixel_data[j][i] (row-major)
+ *   rgb8  W*H*3 uint8  the values writePPMImage prints: min(255,(int)(255*c)) (ppmIO.hpp:150)
+ *   hit   W*H   int32  primary-hit face id, -1 = background
+ * With world > 1 only this rank's tiles are rendered; pixels of other ranks are left
+ * untouched in the host buffers (use the *_device entry points + a gather for full frames). */
+int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8, int32_t *hit,
+               rtp_stats *st);
+
+/* Device-resident variant used by multi-GPU drivers: renders this rank's interleaved screen
+ * tiles into a compact tile-major buffer of float4 (r, g, b, bit-cast primary face id) in
+ * device memory.  d_tiles: rtp_tile_buffer_bytes() bytes of device memory owned by the caller
+ * (e.g. a torch tensor), stream: a cudaStream_t (NULL = default stream).  Asynchronous. */
+size_t rtp_tile_buffer_bytes(int width, int height, int rank, int world);
+int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tiles, void *stream,
+                            rtp_stats *st);
+/* After the per-rank tile buffers have been gathered (NCCL) into d_all = [world][max tile
+ * bytes], scatter them to row-major device planes on the gathering rank.  Any output NULL to
+ * skip.  d_rgb: W*H*3 float, d_rgb8: W*H*3 uint8, d_hit: W*H int32. */
+int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void *d_all,
+                      size_t rank_stride_bytes, void *d_rgb, void *d_rgb8, void *d_hit, void *stream);
+
+/* ---- single-ray API ---------------------------------------------------------------------- */
+typedef enum rtp_ray_mode {
+  RTP_RAYS_SHADE = 0,   /* Flyscene::traceRay(origin, dir, 0, false)  -> rgb n x 3 (flyscene.cpp:317) */
+  RTP_RAYS_CLOSEST = 1, /* calculateMinimumFace -> face n (int32), t n (flyscene.cpp:373)  */
+  RTP_RAYS_ANYHIT = 2   /* shadow(P, L) -> occluded n (uint8)                (flyscene.cpp:510)  */
+} rtp_ray_mode;
+/* rays: n x 6 floats (origin, direction) in HOST memory; outputs in host memory. */
+int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max_depth,
+                   const float background[3], float *rgb, int32_t *face, float *t, uint8_t *occluded,
+                   rtp_stats *st);
+/* Same with rays and outputs already resident on the device (bench / AO stress). */
+int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode, void *d_face,
+                          void *d_t, void *d_occluded, void *stream, rtp_stats *st);
+
+/* ---- introspection ------------------------------------------------------------------------ */
+/* BoundingBox::boxes view of the scene (BoundingBox.h:13): sizes, then copies. */
+int rtp_scene_box_count(const rtp_scene *s);
+int rtp_scene_get_boxes(const rtp_scene *s, float *boxes /* B x 6 */, int32_t *box_off /* B+1 */,
+                        int32_t *box_faces /* F */);
+int rtp_scene_info(const rtp_scene *s, rtp_stats *st);
+const char *rtp_last_error(void);
+int rtp_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTP_H */

@@ -1,0 +1,525 @@
+// rtp_api.cu - the C ABI of include/rtp.h: scene upload, frame buffers, kernel sequencing.
+// There is no CPU fallback here: every compute entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/rtp.h"
+#include "rtp_kernels.h"
+#include "scene_host.h"
+
+using namespace rtp;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string &msg) {
+  g_err = msg;
+  return code;
+}
+
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(RTP_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));           \
+  } while (0)
+
+template <class T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;
+  ~DevBuf() { release(); }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  cudaError_t ensure(size_t count) {
+    if (count <= n && p) return cudaSuccess;
+    release();
+    cudaError_t e = cudaMalloc((void **)&p, std::max<size_t>(count, 1) * sizeof(T));
+    if (e == cudaSuccess) n = count;
+    return e;
+  }
+  cudaError_t upload(const std::vector<T> &v, cudaStream_t st) {
+    cudaError_t e = ensure(v.size());
+    if (e != cudaSuccess) return e;
+    if (v.empty()) return cudaSuccess;
+    return cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+  }
+};
+
+struct Frame {
+  int width = 0, height = 0, rank = 0, world = 1, max_depth = 0;
+  int n_px = 0, tiles_x = 0;
+  DevBuf<float4> fb, ksdeep, direct, ray_o0, ray_o1, ray_d0, ray_d1;
+  DevBuf<int> primface, hit_slot, tile_ids, local_of_tile;
+  DevBuf<float> hit_t;
+  DevBuf<float> out_rgb;
+  DevBuf<unsigned char> out_rgb8;
+  DevBuf<int> out_hit;
+};
+
+}  // namespace
+
+struct rtp_scene {
+  int device = 0;
+  HostScene host;
+  DevBuf<float4> nodes, tris, vnorm, boxes, materials, lights;
+  DevBuf<int> face_of;
+  DevBuf<int> counters;
+  DevBuf<unsigned long long> stats;
+  DeviceScene dS;
+  DeviceCamera cam;
+  bool have_camera = false, have_lights = false;
+  LaunchCfg cfg;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  Frame frame;   // pixel frames (camera rays)
+  Frame rframe;  // ray-batch frames (rtp_trace_rays SHADE)
+  DevBuf<float> rays_dev;
+  DevBuf<int> rays_face;
+  DevBuf<float> rays_t;
+  DevBuf<unsigned char> rays_occ;
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+const char *rtp_last_error(void) { return g_err.c_str(); }
+int rtp_abi_version(void) { return RTP_ABI_VERSION; }
+
+int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
+  if (!mesh || !out) return fail(RTP_ERR_INVALID, "rtp_scene_create: null argument");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(RTP_ERR_CUDA, std::string("rtp_scene_create: no CUDA device (") +
+                                  (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                                  "); this library has no CPU fallback");
+  if (device < 0) CK(cudaGetDevice(&device));
+  if (device >= ndev) return fail(RTP_ERR_INVALID, "rtp_scene_create: device ordinal out of range");
+  rtp_scene *s = new (std::nothrow) rtp_scene();
+  if (!s) return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory");
+  s->device = device;
+  std::string msg;
+  try {
+    msg = flatten_scene(*mesh, s->host);
+  } catch (const std::bad_alloc &) {
+    delete s;
+    return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory while flattening");
+  }
+  if (!msg.empty()) {
+    delete s;
+    return fail(RTP_ERR_INVALID, msg);
+  }
+  DeviceGuard g(device);
+  if (!g.ok) { delete s; return fail(RTP_ERR_CUDA, "rtp_scene_create: cudaSetDevice failed"); }
+  auto cleanup = [&](cudaError_t err, const char *what) {
+    std::string m = std::string(what) + ": " + cudaGetErrorString(err);
+    delete s;
+    return fail(RTP_ERR_CUDA, m);
+  };
+  if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return cleanup(e, "cudaStreamCreate");
+  for (auto &ev : s->ev)
+    if ((e = cudaEventCreate(&ev)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
+  HostScene &h = s->host;
+  if ((e = s->nodes.upload(h.nodes, s->stream)) != cudaSuccess) return cleanup(e, "upload nodes");
+  if ((e = s->tris.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
+  if ((e = s->vnorm.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
+  if ((e = s->boxes.upload(h.boxes, s->stream)) != cudaSuccess) return cleanup(e, "upload boxes");
+  if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
+  if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
+  if ((e = s->counters.ensure(kCtrInts)) != cudaSuccess) return cleanup(e, "alloc counters");
+  if ((e = s->stats.ensure(kStatCount)) != cudaSuccess) return cleanup(e, "alloc stats");
+  if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
+  // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
+  std::vector<float4>().swap(h.nodes);
+  std::vector<float4>().swap(h.tris);
+  std::vector<float4>().swap(h.vnorm);
+  DeviceScene &d = s->dS;
+  d.nodes = s->nodes.p; d.tris = s->tris.p; d.vnorm = s->vnorm.p; d.boxes = s->boxes.p;
+  d.face_of = s->face_of.p; d.materials = s->materials.p; d.lights = nullptr; d.n_lights = 0;
+  std::memcpy(d.minv, h.minv, sizeof d.minv);
+  d.n_tris = h.n_tris; d.n_nodes = h.n_nodes; d.n_boxes = h.n_boxes;
+  query_launch_cfg(device, s->cfg);
+  if ((e = cudaGetLastError()) != cudaSuccess) return cleanup(e, "query_launch_cfg");
+  *out = s;
+  return RTP_OK;
+}
+
+int rtp_scene_destroy(rtp_scene *s) {
+  if (!s) return RTP_OK;
+  DeviceGuard g(s->device);
+  if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+  for (auto &ev : s->ev)
+    if (ev) cudaEventDestroy(ev);
+  delete s;  // DevBuf destructors free device memory while the device is current
+  return RTP_OK;
+}
+
+int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
+  if (!s || !l) return fail(RTP_ERR_INVALID, "rtp_set_lights: null argument");
+  if (l->n_point < 0 || l->n_dir < 0 || (l->n_point && !l->point) || (l->n_dir && !l->dir))
+    return fail(RTP_ERR_INVALID, "rtp_set_lights: bad light arrays");
+  DeviceGuard g(s->device);
+  std::vector<float4> packed;
+  pack_lights(*l, packed);
+  CK(s->lights.upload(packed, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  s->dS.lights = s->lights.p;
+  s->dS.n_lights = l->n_point + l->n_dir;
+  s->have_lights = true;
+  return RTP_OK;
+}
+
+int rtp_set_camera(rtp_scene *s, const rtp_camera *c) {
+  if (!s || !c) return fail(RTP_ERR_INVALID, "rtp_set_camera: null argument");
+  if (!(c->viewport[2] > 0.f) || !(c->viewport[3] > 0.f)) return fail(RTP_ERR_INVALID, "rtp_set_camera: empty viewport");
+  derive_camera(*c, s->cam);
+  s->have_camera = true;
+  return RTP_OK;
+}
+
+int rtp_scene_box_count(const rtp_scene *s) { return s ? s->host.n_boxes : 0; }
+
+int rtp_scene_get_boxes(const rtp_scene *s, float *boxes, int32_t *box_off, int32_t *box_faces) {
+  if (!s) return fail(RTP_ERR_INVALID, "rtp_scene_get_boxes: null scene");
+  const HostScene &h = s->host;
+  if (boxes) std::memcpy(boxes, h.box_bounds.data(), h.box_bounds.size() * sizeof(float));
+  if (box_off) std::memcpy(box_off, h.box_off.data(), h.box_off.size() * sizeof(int32_t));
+  if (box_faces) std::memcpy(box_faces, h.box_faces.data(), h.box_faces.size() * sizeof(int32_t));
+  return RTP_OK;
+}
+
+int rtp_scene_info(const rtp_scene *s, rtp_stats *st) {
+  if (!s || !st) return fail(RTP_ERR_INVALID, "rtp_scene_info: null argument");
+  std::memset(st, 0, sizeof *st);
+  st->n_bvh_nodes = s->host.n_nodes;
+  st->n_triangles = s->host.n_tris;
+  return RTP_OK;
+}
+
+}  // extern "C"
+
+// ---- frames -------------------------------------------------------------------------------
+namespace {
+
+int own_tile_count(int width, int height, int rank, int world) {
+  const int tx = (width + kTileDim - 1) / kTileDim, ty = (height + kTileDim - 1) / kTileDim;
+  int n = 0;
+  for (int y = 0; y < ty; ++y)
+    for (int x = 0; x < tx; ++x) n += tile_owner(x, y, world) == rank;
+  return n;
+}
+
+int max_tile_count(int width, int height, int world) {
+  int m = 0;
+  for (int r = 0; r < world; ++r) m = std::max(m, own_tile_count(width, height, r, world));
+  return m;
+}
+
+// (Re)allocates the per-frame device state.  n_paths: pixels (tile-padded) or user rays.
+int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int world, int max_depth, int n_paths,
+                 bool with_tiles) {
+  const bool same = f.width == width && f.height == height && f.rank == rank && f.world == world &&
+                    f.max_depth >= max_depth && f.n_px == n_paths;
+  if (same) return RTP_OK;
+  f.width = width; f.height = height; f.rank = rank; f.world = world; f.max_depth = max_depth; f.n_px = n_paths;
+  f.tiles_x = (width + kTileDim - 1) / kTileDim;
+  const size_t n = (size_t)std::max(n_paths, 1);
+  CK(f.ksdeep.ensure(n));
+  CK(f.direct.ensure(n * (size_t)max_depth));
+  CK(f.ray_o0.ensure(n)); CK(f.ray_o1.ensure(n)); CK(f.ray_d0.ensure(n)); CK(f.ray_d1.ensure(n));
+  CK(f.primface.ensure(n)); CK(f.hit_slot.ensure(n)); CK(f.hit_t.ensure(n));
+  if (with_tiles) {
+    std::vector<int32_t> tiles, local;
+    tile_tables(width, height, rank, world, tiles, local);
+    CK(f.tile_ids.upload(tiles, s->stream));
+    CK(f.local_of_tile.upload(local, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+  }
+  return RTP_OK;
+}
+
+void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, FrameParams &p) {
+  p.S = s->dS;
+  p.cam = s->cam;
+  p.width = f.width; p.height = f.height; p.tiles_x = f.tiles_x; p.n_px = f.n_px;
+  p.tile_ids = f.tile_ids.p;
+  p.user_rays = nullptr; p.n_user_rays = 0;
+  p.max_depth = o.max_depth;
+  p.bg[0] = o.background[0]; p.bg[1] = o.background[1]; p.bg[2] = o.background[2];
+  p.fb = fb;
+  p.primface = f.primface.p; p.ksdeep = f.ksdeep.p; p.direct = f.direct.p;
+  p.ray_o[0] = f.ray_o0.p; p.ray_o[1] = f.ray_o1.p; p.ray_d[0] = f.ray_d0.p; p.ray_d[1] = f.ray_d1.p;
+  p.hit_t = f.hit_t.p; p.hit_slot = f.hit_slot.p;
+  p.counters = s->counters.p; p.stats = s->stats.p;
+}
+
+// Enqueues one frame: 2 * max_depth trace kernels + resolve.  Returns the number of launches.
+int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches) {
+  CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), st));
+  CK(cudaMemsetAsync(s->stats.p, 0, kStatCount * sizeof(unsigned long long), st));
+  int n = 0;
+  for (int d = 0; d < p.max_depth; ++d) {
+    launch_closest(p, d, s->cfg, st);
+    launch_shade(p, d, s->cfg, st);
+    n += 2;
+  }
+  launch_resolve(p, st);
+  ++n;
+  CK(cudaGetLastError());
+  if (launches) *launches = n;
+  return RTP_OK;
+}
+
+int check_render_args(rtp_scene *s, const rtp_render_opts *o) {
+  if (!s || !o) return fail(RTP_ERR_INVALID, "render: null argument");
+  if (o->width <= 0 || o->height <= 0 || (long long)o->width * o->height > (1ll << 30))
+    return fail(RTP_ERR_INVALID, "render: bad image size");
+  if (o->max_depth < 1 || o->max_depth > kMaxDepth) return fail(RTP_ERR_INVALID, "render: max_depth must be in [1, 8]");
+  if (o->world < 1 || o->rank < 0 || o->rank >= o->world) return fail(RTP_ERR_INVALID, "render: bad rank/world");
+  if (!s->have_camera) return fail(RTP_ERR_STATE, "render: rtp_set_camera has not been called");
+  if (!s->have_lights) return fail(RTP_ERR_STATE, "render: rtp_set_lights has not been called");
+  return RTP_OK;
+}
+
+int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
+  unsigned long long h[kStatCount];
+  CK(cudaMemcpyAsync(h, s->stats.p, sizeof h, cudaMemcpyDeviceToHost, stream));
+  CK(cudaStreamSynchronize(stream));
+  st->rays_primary = (int64_t)h[kStatPrimary];
+  st->rays_shadow = (int64_t)h[kStatShadow];
+  st->rays_reflection = (int64_t)h[kStatReflection];
+  st->hits = (int64_t)h[kStatHits];
+  st->n_bvh_nodes = s->host.n_nodes;
+  st->n_triangles = s->host.n_tris;
+  return RTP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t rtp_tile_buffer_bytes(int width, int height, int rank, int world) {
+  if (width <= 0 || height <= 0 || world < 1) return 0;
+  // every rank's buffer is padded to the largest tile count so that a plain gather works
+  (void)rank;
+  return (size_t)max_tile_count(width, height, world) * kTilePixels * sizeof(float4);
+}
+
+int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tiles, void *stream, rtp_stats *st) {
+  int rc = check_render_args(s, o);
+  if (rc) return rc;
+  if (!d_tiles) return fail(RTP_ERR_INVALID, "rtp_render_tiles_device: null tile buffer");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
+  rc = ensure_frame(s, s->frame, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
+  if (rc) return rc;
+  FrameParams p;
+  fill_params(s, s->frame, *o, (float4 *)d_tiles, p);
+  int launches = 0;
+  if (st) CK(cudaEventRecord(s->ev[0], cs));
+  rc = enqueue_frame(s, p, cs, &launches);
+  if (rc) return rc;
+  if (st) {
+    CK(cudaEventRecord(s->ev[1], cs));
+    std::memset(st, 0, sizeof *st);
+    rc = read_stats(s, st, cs);
+    if (rc) return rc;
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
+    st->ms_total = st->ms_trace;
+    st->kernel_launches = launches;
+  }
+  return RTP_OK;
+}
+
+int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void *d_all, size_t rank_stride_bytes,
+                      void *d_rgb, void *d_rgb8, void *d_hit, void *stream) {
+  if (!s || !d_all || width <= 0 || height <= 0 || world < 1) return fail(RTP_ERR_INVALID, "rtp_untile_device: bad argument");
+  if (rank_stride_bytes % sizeof(float4)) return fail(RTP_ERR_INVALID, "rtp_untile_device: stride must be a multiple of 16");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  Frame &f = s->frame;
+  if (f.width != width || f.height != height || f.world != world || !f.local_of_tile.p)
+    return fail(RTP_ERR_STATE, "rtp_untile_device: render a frame of this size/world first");
+  launch_untile((const float4 *)d_all, rank_stride_bytes / sizeof(float4), f.local_of_tile.p, width, height, world, -1,
+                (float *)d_rgb, (unsigned char *)d_rgb8, (int *)d_hit, cs);
+  CK(cudaGetLastError());
+  return RTP_OK;
+}
+
+int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8, int32_t *hit, rtp_stats *st) {
+  int rc = check_render_args(s, o);
+  if (rc) return rc;
+  DeviceGuard g(s->device);
+  cudaStream_t cs = s->stream;
+  Frame &f = s->frame;
+  const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
+  rc = ensure_frame(s, f, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
+  if (rc) return rc;
+  CK(f.fb.ensure((size_t)std::max(n_px, 1)));
+  const size_t npix = (size_t)o->width * o->height;
+  if (rgb) CK(f.out_rgb.ensure(npix * 3));
+  if (rgb8) CK(f.out_rgb8.ensure(npix * 3));
+  if (hit) CK(f.out_hit.ensure(npix));
+  FrameParams p;
+  fill_params(s, f, *o, f.fb.p, p);
+  int launches = 0;
+  CK(cudaEventRecord(s->ev[0], cs));
+  rc = enqueue_frame(s, p, cs, &launches);
+  if (rc) return rc;
+  CK(cudaEventRecord(s->ev[1], cs));
+  if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
+    if (rgb) CK(cudaMemcpyAsync(f.out_rgb.p, rgb, npix * 3 * sizeof(float), cudaMemcpyHostToDevice, cs));
+    if (rgb8) CK(cudaMemcpyAsync(f.out_rgb8.p, rgb8, npix * 3, cudaMemcpyHostToDevice, cs));
+    if (hit) CK(cudaMemcpyAsync(f.out_hit.p, hit, npix * sizeof(int), cudaMemcpyHostToDevice, cs));
+  }
+  if (rgb || rgb8 || hit) {
+    launch_untile(f.fb.p, 0, f.local_of_tile.p, o->width, o->height, o->world, o->world > 1 ? o->rank : 0,
+                  rgb ? f.out_rgb.p : nullptr, rgb8 ? f.out_rgb8.p : nullptr, hit ? f.out_hit.p : nullptr, cs);
+    ++launches;
+    CK(cudaGetLastError());
+  }
+  CK(cudaEventRecord(s->ev[2], cs));
+  if (rgb) CK(cudaMemcpyAsync(rgb, f.out_rgb.p, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost, cs));
+  if (rgb8) CK(cudaMemcpyAsync(rgb8, f.out_rgb8.p, npix * 3, cudaMemcpyDeviceToHost, cs));
+  if (hit) CK(cudaMemcpyAsync(hit, f.out_hit.p, npix * sizeof(int), cudaMemcpyDeviceToHost, cs));
+  CK(cudaStreamSynchronize(cs));
+  if (st) {
+    std::memset(st, 0, sizeof *st);
+    rc = read_stats(s, st, cs);
+    if (rc) return rc;
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
+    CK(cudaEventElapsedTime(&st->ms_total, s->ev[0], s->ev[2]));
+    st->kernel_launches = launches;
+  }
+  return RTP_OK;
+}
+
+int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode, void *d_face, void *d_t,
+                          void *d_occluded, void *stream, rtp_stats *st) {
+  if (!s || !d_rays || n < 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: bad argument");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  int *cursor = s->counters.p + kCtrAux;
+  CK(cudaMemsetAsync(cursor, 0, sizeof(int), cs));
+  if (st) CK(cudaEventRecord(s->ev[0], cs));
+  if (mode == RTP_RAYS_CLOSEST) {
+    if (!d_face) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: face output required");
+    launch_rays_closest(s->dS, (const float *)d_rays, n, (int *)d_face, (float *)d_t, cursor, s->cfg, cs);
+  } else if (mode == RTP_RAYS_ANYHIT) {
+    if (!d_occluded) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: occluded output required");
+    launch_rays_anyhit(s->dS, (const float *)d_rays, n, (unsigned char *)d_occluded, cursor, s->cfg, cs);
+  } else {
+    return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: mode must be CLOSEST or ANYHIT");
+  }
+  CK(cudaGetLastError());
+  if (st) {
+    CK(cudaEventRecord(s->ev[1], cs));
+    CK(cudaStreamSynchronize(cs));
+    std::memset(st, 0, sizeof *st);
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
+    st->ms_total = st->ms_trace;
+    st->kernel_launches = 1;
+    (mode == RTP_RAYS_ANYHIT ? st->rays_shadow : st->rays_primary) = n;
+    st->n_bvh_nodes = s->host.n_nodes;
+    st->n_triangles = s->host.n_tris;
+  }
+  return RTP_OK;
+}
+
+int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max_depth, const float background[3],
+                   float *rgb, int32_t *face, float *t, uint8_t *occluded, rtp_stats *st) {
+  if (!s || !rays || n <= 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays: bad argument");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = s->stream;
+  CK(s->rays_dev.ensure((size_t)n * 6));
+  CK(cudaMemcpyAsync(s->rays_dev.p, rays, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, cs));
+  if (mode == RTP_RAYS_CLOSEST) {
+    if (!face) return fail(RTP_ERR_INVALID, "rtp_trace_rays: face output required");
+    CK(s->rays_face.ensure((size_t)n));
+    CK(s->rays_t.ensure((size_t)n));
+    int rc = rtp_trace_rays_device(s, s->rays_dev.p, n, mode, s->rays_face.p, s->rays_t.p, nullptr, cs, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(face, s->rays_face.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, cs));
+    if (t) CK(cudaMemcpyAsync(t, s->rays_t.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, cs));
+    CK(cudaStreamSynchronize(cs));
+    return RTP_OK;
+  }
+  if (mode == RTP_RAYS_ANYHIT) {
+    if (!occluded) return fail(RTP_ERR_INVALID, "rtp_trace_rays: occluded output required");
+    CK(s->rays_occ.ensure((size_t)n));
+    int rc = rtp_trace_rays_device(s, s->rays_dev.p, n, mode, nullptr, nullptr, s->rays_occ.p, cs, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(occluded, s->rays_occ.p, (size_t)n, cudaMemcpyDeviceToHost, cs));
+    CK(cudaStreamSynchronize(cs));
+    return RTP_OK;
+  }
+  if (mode != RTP_RAYS_SHADE) return fail(RTP_ERR_INVALID, "rtp_trace_rays: unknown mode");
+  // Flyscene::traceRay for arbitrary rays: the frame pipeline with caller-supplied depth-0 rays
+  if (!rgb) return fail(RTP_ERR_INVALID, "rtp_trace_rays: rgb output required");
+  if (max_depth < 1 || max_depth > kMaxDepth) return fail(RTP_ERR_INVALID, "rtp_trace_rays: max_depth must be in [1, 8]");
+  if (!s->have_lights) return fail(RTP_ERR_STATE, "rtp_trace_rays: rtp_set_lights has not been called");
+  Frame &f = s->rframe;
+  int rc = ensure_frame(s, f, 0, 0, 0, 1, std::max(max_depth, 1), (int)n, false);
+  if (rc) return rc;
+  CK(f.fb.ensure((size_t)n));
+  rtp_render_opts o;
+  std::memset(&o, 0, sizeof o);
+  o.max_depth = max_depth;
+  const float bgdef[3] = {(float)0.9, (float)0.9, (float)0.9};
+  std::memcpy(o.background, background ? background : bgdef, sizeof o.background);
+  FrameParams p;
+  fill_params(s, f, o, f.fb.p, p);
+  std::memset(&p.cam, 0, sizeof p.cam);
+  p.user_rays = s->rays_dev.p;
+  p.n_user_rays = (int)n;
+  int launches = 0;
+  CK(cudaEventRecord(s->ev[0], cs));
+  rc = enqueue_frame(s, p, cs, &launches);
+  if (rc) return rc;
+  CK(cudaEventRecord(s->ev[1], cs));
+  std::vector<float4> h((size_t)n);
+  CK(cudaMemcpyAsync(h.data(), f.fb.p, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, cs));
+  CK(cudaStreamSynchronize(cs));
+  for (int64_t i = 0; i < n; ++i) {
+    rgb[3 * i] = h[(size_t)i].x; rgb[3 * i + 1] = h[(size_t)i].y; rgb[3 * i + 2] = h[(size_t)i].z;
+    if (face) std::memcpy(&face[i], &h[(size_t)i].w, 4);
+  }
+  if (st) {
+    std::memset(st, 0, sizeof *st);
+    rc = read_stats(s, st, cs);
+    if (rc) return rc;
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
+    st->ms_total = st->ms_trace;
+    st->kernel_launches = launches;
+  }
+  return RTP_OK;
+}
+
+}  // extern "C"

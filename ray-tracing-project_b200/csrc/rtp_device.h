@@ -1,0 +1,243 @@
+// rtp_device.h - device-side scene layout, BVH traversal and the reference's exact
+// ray/triangle, ray/BoundingBox and shading arithmetic.
+//
+// Everything here is __host__ __device__: the CUDA kernels (rtp_kernels.cu) are the product;
+// tests/hostsim compiles the same functions with g++ to check them against the oracle on a
+// machine without a GPU (test infrastructure, never linked into the product library).
+//
+// Layout in HBM (all 16-byte aligned, read through the read-only path, L2-resident for
+// scenes up to ~1 M triangles):
+//   nodes  : 4 x float4 per BVH2 node (64 B)  n0 = c0.lo.x c0.hi.x c0.lo.y c0.hi.y
+//                                              n1 = c1.lo.x c1.hi.x c1.lo.y c1.hi.y
+//                                              n2 = c0.lo.z c0.hi.z c1.lo.z c1.hi.z
+//                                              n3 = child0, child1 (int bits), -, -
+//            child >= 0: inner node index; child < 0: leaf, ~child = first_tri << 3 | (count-1)
+//   tris   : 4 x float4 per triangle in leaf order (64 B)
+//                                              T0 = world v0, reference visitation rank
+//                                              T1 = world v1, reference BoundingBox id
+//                                              T2 = world v2, (material id + 1) | flags
+//                                              T3 = unit face normal, plane constant n.v0
+//   vnorm  : 3 x float4 per triangle (48 B): the three unit vertex normals (shading only)
+//   boxes  : 2 x float4 per reference BoundingBox (object-space low / high)
+//   face_of: int per triangle slot -> reference face id
+#pragma once
+#include "rtp_math.h"
+
+// float4 / make_float4 come from the CUDA toolkit's header-only vector types, for nvcc and for
+// plain g++ translation units alike (same 16-byte aligned type everywhere).
+#include <vector_functions.h>
+#include <vector_types.h>
+
+namespace rtp {
+
+constexpr int kStackSize = 64;
+constexpr int kSentinel = 0x7fffffff;
+constexpr unsigned kTriFlagNormalCheck = 0x80000000u;  // vertex normals may cancel: run the Q12 check
+constexpr unsigned kTriMatMask = 0x0000ffffu;
+constexpr int kMaxDepth = 8;   // direct-colour slots per pixel
+constexpr int kTileDim = 32;   // screen tile edge (multi-GPU interleave unit)
+constexpr int kTilePixels = kTileDim * kTileDim;
+
+struct DeviceScene {
+  const float4 *nodes;
+  const float4 *tris;
+  const float4 *vnorm;
+  const float4 *boxes;
+  const int *face_of;
+  const float4 *materials;  // 3 x float4 per entry: (ka, Ns) (kd, -) (ks, -); entry 0 = Flyscene defaults
+  const float4 *lights;     // 2 x float4 per light: (pos-or-vector, is_directional) (rgb, -)
+  float minv[12];           // getShapeModelMatrix().inverse(), 3x4 row-major
+  int n_lights;
+  int n_tris, n_nodes, n_boxes;
+};
+
+struct DeviceCamera {
+  float eye[3];
+  float inv_view[12];
+  float vp[4];
+  float sx, sy;  // aspect_ratio*scale, scale (camera.hpp:166-167)
+};
+
+#if defined(__CUDA_ARCH__)
+#define RTP_LDG4(p) __ldg(p)
+#define RTP_LDGI(p) __ldg(p)
+#else
+#define RTP_LDG4(p) (*(p))
+#define RTP_LDGI(p) (*(p))
+#endif
+
+RTP_HD v3 xyz(float4 a) { return mk3(a.x, a.y, a.z); }
+
+// ---- Camera::screenToWorld + direction (camera.hpp:155-173, flyscene.cpp:308) ----------------
+RTP_HD v3 primary_dir(const DeviceCamera &c, int i, int j) {
+  float ri = (float)i, rj = (float)j;
+  v3 nc;
+  // NDC in double precision, rounded to float when stored in the Vector3f
+  nc.x = (float)(2.0 * (double)fsub(ri, c.vp[0]) / (double)c.vp[2] - 1.0);
+  nc.y = (float)(1.0 - 2.0 * (double)fsub(rj, c.vp[1]) / (double)c.vp[3]);
+  nc.z = -1.0f;
+  nc.x = fmul(nc.x, c.sx);
+  nc.y = fmul(nc.y, c.sy);
+  v3 w = affine_mul(c.inv_view, nc);
+  return vnormalized(vsub(w, mk3(c.eye[0], c.eye[1], c.eye[2])));
+}
+
+// ---- the reference's BoundingBox slab test, exactly (flyscene.cpp:484-507) ------------------
+// Decides whether the reference would have looked at the faces of box `b` at all for this ray.
+RTP_HD bool ref_box_pass(const DeviceScene &S, v3 bo, v3 d, int b) {
+  float4 lo = RTP_LDG4(S.boxes + 2 * b), hi = RTP_LDG4(S.boxes + 2 * b + 1);
+  v3 o2 = affine_mul(S.minv, bo);
+  v3 d2 = vnormalized(linear_mul(S.minv, d));
+  v3 tmin = vsub(xyz(lo), o2), tmax = vsub(xyz(hi), o2);
+  tmin.x = fdiv(tmin.x, d2.x); tmax.x = fdiv(tmax.x, d2.x);
+  tmin.y = fdiv(tmin.y, d2.y); tmax.y = fdiv(tmax.y, d2.y);
+  tmin.z = fdiv(tmin.z, d2.z); tmax.z = fdiv(tmax.z, d2.z);
+  float tin = std_max(std_min(tmin.x, tmax.x), std_max(std_min(tmin.y, tmax.y), std_min(tmin.z, tmax.z)));
+  float tout = std_min(std_max(tmin.x, tmax.x), std_min(std_max(tmin.y, tmax.y), std_max(tmin.z, tmax.z)));
+  return !(tin > tout || tout < 0.f);
+}
+
+// ---- interpolateNormal (flyscene.cpp:572-600) given world vertices and unit vertex normals ----
+RTP_HD v3 interpolate_normal(v3 v0, v3 v1, v3 v2, v3 fn, v3 n0, v3 n1, v3 n2, v3 P) {
+  v3 e0 = vsub(v1, v0), e1 = vsub(v2, v1), e2 = vsub(v0, v2);
+  v3 a0v = vcross(e0, vsub(P, v0)), a1v = vcross(e1, vsub(P, v1)), a2v = vcross(e2, vsub(P, v2));
+  if (vdot(fn, a0v) < 0.f || vdot(fn, a1v) < 0.f || vdot(fn, a2v) < 0.f) return mk3(0.f, 0.f, 0.f);
+  float area0 = fdiv(vnorm(a0v), 2.f), area1 = fdiv(vnorm(a1v), 2.f), area2 = fdiv(vnorm(a2v), 2.f);
+  float area = fdiv(vnorm(vcross(e0, vneg(e2))), 2.f);
+  v3 s = vadd(vadd(vdivs(vmuls(n0, area1), area), vdivs(vmuls(n1, area2), area)), vdivs(vmuls(n2, area0), area));
+  return vnormalized(s);
+}
+
+RTP_HD v3 interpolate_normal_slot(const DeviceScene &S, int slot, v3 P) {
+  const float4 *T = S.tris + 4 * (size_t)slot;
+  const float4 *N = S.vnorm + 3 * (size_t)slot;
+  return interpolate_normal(xyz(RTP_LDG4(T)), xyz(RTP_LDG4(T + 1)), xyz(RTP_LDG4(T + 2)), xyz(RTP_LDG4(T + 3)),
+                            xyz(RTP_LDG4(N)), xyz(RTP_LDG4(N + 1)), xyz(RTP_LDG4(N + 2)), P);
+}
+
+// ---- calculateDistance (flyscene.cpp:444-478) on one flattened triangle ----------------------
+// Returns true when the reference would report t >= 0 for this face, with 0 <= t <= tmax.
+RTP_HD bool tri_exact(const DeviceScene &S, int slot, v3 o, v3 d, float tmax, float &t_out, float4 &T0o, float4 &T1o) {
+  const float4 *T = S.tris + 4 * (size_t)slot;
+  float4 T3 = RTP_LDG4(T + 3);
+  v3 n = xyz(T3);
+  float dn = vdot(n, d);
+  if (dn == 0.f) return false;                       // :453
+  float t = fdiv(fsub(T3.w, vdot(o, n)), dn);         // :459-463
+  if (!(t >= 0.f) || t > tmax) return false;           // caller's 0 <= t (< best) test, :387
+  v3 P = vadd(o, vmuls(d, t));                        // :464
+  float4 T0 = RTP_LDG4(T), T1 = RTP_LDG4(T + 1), T2 = RTP_LDG4(T + 2);
+  v3 v0 = xyz(T0), v1 = xyz(T1), v2 = xyz(T2);
+  v3 e0 = vsub(v1, v0), e1 = vsub(v2, v1), e2 = vsub(v0, v2);
+  if (vdot(n, vcross(e0, vsub(P, v0))) < 0.f) return false;   // :591
+  if (vdot(n, vcross(e1, vsub(P, v1))) < 0.f) return false;
+  if (vdot(n, vcross(e2, vsub(P, v2))) < 0.f) return false;
+  if ((unsigned)f2i(T2.w) & kTriFlagNormalCheck) {            // :467 (only when it can trigger)
+    const float4 *N = S.vnorm + 3 * (size_t)slot;
+    v3 nn = interpolate_normal(v0, v1, v2, n, xyz(RTP_LDG4(N)), xyz(RTP_LDG4(N + 1)), xyz(RTP_LDG4(N + 2)), P);
+    if (vnorm(nn) == 0.f) return false;
+  }
+  t_out = t;
+  T0o = T0; T1o = T1;
+  return true;
+}
+
+// ---- BVH2 traversal ---------------------------------------------------------------------------
+// ANY = false: calculateMinimumFace (flyscene.cpp:373-396): smallest t >= 0 over the faces of
+//   every reference box whose slab test passes, ties to the lowest visitation rank.
+// ANY = true : shadow (flyscene.cpp:510-526): any such face.
+// o/d: origin and direction used for the face tests; bo: origin used for the reference box test
+// (== o for closest-hit, the un-offset point P for shadow rays).
+template <bool ANY>
+RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int &best_slot) {
+  const float ooeps = 1.0e-24f;
+  float dx = fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x);
+  float dy = fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y);
+  float dz = fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z);
+  const float idx = 1.0f / dx, idy = 1.0f / dy, idz = 1.0f / dz;
+  const float oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
+  int stack[kStackSize];
+  int sp = 0;
+  stack[0] = kSentinel;
+  int node = 0;  // root is always an inner node
+  float tbest = INFINITY;
+  unsigned rbest = 0xffffffffu;
+  int sbest = -1;
+  while (node != kSentinel) {
+    while (node >= 0 && node != kSentinel) {
+      const float4 *Np = S.nodes + 4 * (size_t)node;
+      float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
+      float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
+      float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
+      float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
+      float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
+      float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
+      float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
+      float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.f));
+      float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), tbest));
+      float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.f));
+      float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), tbest));
+      bool h0 = c0min <= c0max, h1 = c1min <= c1max;
+      int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
+      if (!h0 && !h1) {
+        node = stack[sp];
+        sp = sp > 0 ? sp - 1 : 0;
+      } else {
+        node = h0 ? ch0 : ch1;
+        if (h0 && h1) {
+          if (c1min < c0min) { int tmp = node; node = ch1; ch1 = tmp; }
+          stack[++sp] = ch1;
+        }
+      }
+    }
+    while (node < 0) {
+      int enc = ~node;
+      int first = enc >> 3, cnt = (enc & 7) + 1;
+      for (int k = 0; k < cnt; ++k) {
+        float t;
+        float4 T0, T1;
+        if (!tri_exact(S, first + k, o, d, tbest, t, T0, T1)) continue;
+        unsigned rank = (unsigned)f2i(T0.w);
+        // t <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
+        // and t == +inf never beats the initial INFINITY.
+        if (!ANY && !(t < tbest || (sbest >= 0 && rank < rbest))) continue;
+        if (!ref_box_pass(S, bo, d, f2i(T1.w))) continue;      // face not visible to the reference
+        tbest = t; rbest = rank; sbest = first + k;
+        if (ANY) { best_t = t; best_slot = sbest; return true; }
+      }
+      node = stack[sp];
+      sp = sp > 0 ? sp - 1 : 0;
+    }
+  }
+  best_t = tbest;
+  best_slot = sbest;
+  return sbest >= 0;
+}
+
+// ---- calcSingleColor after the shadow gate (flyscene.cpp:546-565) -----------------------------
+RTP_HD v3 phong(v3 ka, v3 kd, v3 ks, float shininess, v3 normal, v3 L, v3 I, v3 origin, v3 P) {
+  v3 lightReflection = vsub(L, vmuls(normal, fmul(2.f, vdot(normal, L))));
+  v3 eye = vnormalized(vsub(origin, P));
+  v3 ambient = mk3(fmul(I.x, ka.x), fmul(I.y, ka.y), fmul(I.z, ka.z));
+  v3 diffuse = vmuls(mk3(fmul(I.x, kd.x), fmul(I.y, kd.y), fmul(I.z, kd.z)), std_max(vdot(L, normal), 0.f));
+  float sp = std_max(powf(vdot(lightReflection, eye), shininess), 0.f);
+  v3 specular = vmuls(mk3(fmul(I.x, ks.x), fmul(I.y, ks.y), fmul(I.z, ks.z)), sp);
+  return vadd(vadd(ambient, diffuse), specular);
+}
+
+// Flyscene::reflect on dir.normalized() (flyscene.cpp:361,480-482)
+RTP_HD v3 reflect_dir(v3 dir, v3 n) {
+  v3 dn = vnormalized(dir);
+  return vnormalized(vsub(dn, vmuls(vmuls(n, vdot(dn, n)), 2.f)));
+}
+
+// local pixel index -> position inside a 32x32 screen tile: 8x4-pixel warp footprints
+RTP_HD void tile_pixel(int p, int &x, int &y) {
+  int sub = p >> 5, lane = p & 31;
+  x = ((sub & 3) << 3) + (lane & 7);
+  y = ((sub >> 2) << 2) + (lane >> 3);
+}
+// owner rank of screen tile (tx, ty): diagonal interleave
+RTP_HD int tile_owner(int tx, int ty, int world) { return (tx + ty) % world; }
+
+}  // namespace rtp

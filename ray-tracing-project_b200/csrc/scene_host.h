@@ -1,0 +1,44 @@
+// scene_host.h - host-side flattening of the reference's mesh into the device layout
+// (rtp_device.h) plus the BVH over it.  Pure C++ (no CUDA) so tests/hostsim can reuse it.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../include/rtp.h"
+#include "bvh_build.h"
+#include "rtp_device.h"
+
+namespace rtp {
+
+struct HostScene {
+  std::vector<float4> nodes;      // 4 per node
+  std::vector<float4> tris;       // 4 per triangle, leaf order
+  std::vector<float4> vnorm;      // 3 per triangle, leaf order
+  std::vector<float4> boxes;      // 2 per reference box
+  std::vector<int32_t> face_of;   // slot -> face id
+  std::vector<float4> materials;  // 3 per entry, entry 0 = Flyscene defaults (material_id -1)
+  float minv[12];
+  // reference BoundingBox list (kept for rtp_scene_get_boxes)
+  std::vector<float> box_bounds;  // B x 6
+  std::vector<int32_t> box_off, box_faces;
+  int n_tris = 0, n_nodes = 0, n_boxes = 0, bvh_depth = 0;
+  int n_flagged = 0;     // triangles that need the zero-normal check
+  int n_degenerate = 0;  // triangles whose face normal is not finite/unit (edge-case list)
+  float pad = 0.f;       // AABB padding used
+};
+
+// Returns "" on success, else an error message.
+std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads = 0);
+
+// Camera::getCenter, getViewMatrix().inverse(), perspective scale (camera.hpp:115-118,155-173,263-266)
+void derive_camera(const rtp_camera &c, DeviceCamera &out);
+
+// Flyscene::lights then dirLights, in the order calculateColor visits them (flyscene.cpp:606-612)
+void pack_lights(const rtp_lights &l, std::vector<float4> &out);
+
+// Screen tiles owned by `rank` in increasing tile id; local_of_tile[tile id] = index within the owner
+void tile_tables(int width, int height, int rank, int world, std::vector<int32_t> &tiles_of_rank,
+                 std::vector<int32_t> &local_of_tile);
+
+}  // namespace rtp

@@ -1,0 +1,139 @@
+"""Shared test plumbing.  `-m "not gpu"` runs on a CPU-only box (oracle, host logic, ABI surface);
+`-m gpu` runs the parity tests proper through the C ABI on a B200."""
+import ctypes as C
+import glob
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200)")
+
+
+def load_rtp():
+    return importlib.import_module("ray-tracing-project_b200")
+
+
+@pytest.fixture(scope="session")
+def rtp():
+    return load_rtp()
+
+
+@pytest.fixture(scope="session")
+def po():
+    import pyoracle
+    pyoracle.lib()
+    return pyoracle
+
+
+def golden_cases():
+    return sorted(os.path.basename(p)[5:-4] for p in glob.glob(os.path.join(GOLDEN, "case_*.npz")))
+
+
+def load_case(name):
+    return dict(np.load(os.path.join(GOLDEN, f"case_{name}.npz")))
+
+
+_mesh_cache = {}
+
+
+def load_golden_mesh(model):
+    """Mesh arrays as the reference's loader left them (tests/golden/make_golden.py)."""
+    import pyoracle
+    key = str(model).replace(".obj", "")
+    if key not in _mesh_cache:
+        z = np.load(os.path.join(GOLDEN, f"mesh_{key}.npz"))
+        m = pyoracle.Mesh(z["verts"], z["normals"], z["faces"], z["face_mat"], z["materials"], None, z["shape"])
+        m.set_boxes(z["boxes"], z["box_off"], z["box_faces"])
+        m.face_normal_crc = int(z["face_normal_crc"][0])
+        _mesh_cache[key] = m
+    return _mesh_cache[key]
+
+
+def bits_equal(a, b):
+    """Bit-exact float comparison that treats NaN == NaN."""
+    a, b = np.asarray(a, np.float32), np.asarray(b, np.float32)
+    return (a.view(np.int32) == b.view(np.int32)) | (np.isnan(a) & np.isnan(b))
+
+
+HOSTSIM = os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")
+
+
+@pytest.fixture(scope="session")
+def hostsim():
+    """tests/hostsim: the product's __host__ __device__ code compiled for the CPU (test-only)."""
+    csrc = os.path.join(ROOT, "ray-tracing-project_b200", "csrc")
+    srcs = [os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp")] + [os.path.join(csrc, f) for f in
+                                                                      ("scene_host.cpp", "bvh_build.cpp", "ref_boxes.cpp")]
+    deps = srcs + glob.glob(os.path.join(csrc, "*.h"))
+    if not os.path.exists(HOSTSIM) or any(os.path.getmtime(d) > os.path.getmtime(HOSTSIM) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
+                               "-I/usr/local/cuda/include", "-o", HOSTSIM] + srcs + ["-lpthread"])
+    H = C.CDLL(HOSTSIM)
+    H.hostsim_create.restype = C.c_char_p
+    return H
+
+
+class HostSimScene:
+    def __init__(self, H, rtp, mesh, with_boxes=False):
+        self.H, self.rtp = H, rtp
+        kw = dict(boxes=mesh.boxes, box_off=mesh.box_off, box_faces=mesh.box_faces) if with_boxes else {}
+        ms, self._keep = rtp.make_mesh_struct(mesh.verts, mesh.normals, mesh.faces, mesh.face_mat, mesh.materials,
+                                              mesh.shape, None, **kw)
+        self.h = C.c_void_p()
+        err = H.hostsim_create(C.byref(ms), C.byref(self.h))
+        assert not err, err
+        info = (C.c_int * 6)()
+        H.hostsim_info(self.h, info)
+        self.info = dict(zip(("n_tris", "n_nodes", "n_boxes", "depth", "flagged", "degenerate"), list(info)))
+        self.n_faces = len(mesh.faces)
+
+    def boxes(self):
+        nb = self.info["n_boxes"]
+        bb, off, bf = np.zeros((nb, 6), np.float32), np.zeros(nb + 1, np.int32), np.zeros(self.n_faces, np.int32)
+        self.H.hostsim_get_boxes(self.h, bb.ctypes.data_as(C.c_void_p), off.ctypes.data_as(C.c_void_p),
+                                 bf.ctypes.data_as(C.c_void_p))
+        return bb, off, bf
+
+    def render(self, w, h, view, max_depth, point, dirl, pixels=None):
+        import pyoracle
+        l, keep = self.rtp.make_lights_struct(point, dirl)
+        self.H.hostsim_set_lights(self.h, C.byref(l))
+        cam = self.rtp.make_camera_struct(w, h, view)
+        px = pyoracle.all_pixels(w, h) if pixels is None else np.ascontiguousarray(pixels, np.int32)
+        n = len(px)
+        rgb, hit = np.zeros((n, 3), np.float32), np.zeros(n, np.int32)
+        t, d, cnt = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros(4, np.int64)
+        bg = self.rtp.BACKGROUND
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.H.hostsim_render(self.h, C.byref(cam), vp(px), C.c_longlong(n), max_depth, vp(bg), vp(rgb), vp(hit),
+                              vp(t), vp(d), vp(cnt))
+        return dict(rgb=rgb, hit=hit, t=t, dir=d, counts=cnt)
+
+    def rays(self, rays, anyhit):
+        rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 6)
+        out, t = np.zeros(len(rays), np.int32), np.zeros(len(rays), np.float32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.H.hostsim_rays(self.h, vp(rays), C.c_longlong(len(rays)), int(anyhit), vp(out), vp(t))
+        return out, t
+
+    def close(self):
+        self.H.hostsim_destroy(self.h)
+
+
+def has_cuda():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False

@@ -1,0 +1,84 @@
+"""Host-side logic of the product (flatten, BoundingBox splitter, BVH build) and the shared
+__host__ __device__ traversal / intersection / shading code, run on the CPU through
+tests/hostsim (test-only build) and compared bit-for-bit with the reference goldens and the
+oracle.  The CUDA kernels call exactly these functions; the GPU parity tests are in
+test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+from conftest import HostSimScene, bits_equal, golden_cases, load_case, load_golden_mesh
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_shared_device_code_matches_golden(hostsim, rtp, name):
+    c = load_case(name)
+    m = load_golden_mesh(c["model"])
+    s = HostSimScene(hostsim, rtp, m)
+    o = s.render(int(c["w"]), int(c["h"]), c["view"], int(c["max_depth"]), c["point_lights"], c["dir_lights"])
+    s.close()
+    assert bits_equal(o["dir"], c["dir"]).all()
+    assert np.array_equal(o["hit"], c["hit"])
+    assert bits_equal(o["t"], c["t"]).all()
+    assert bits_equal(o["rgb"], c["rgb"]).all()
+    assert o["counts"].tolist() == c["counts"].tolist()
+
+
+@pytest.mark.parametrize("model", ["plane", "cube", "testding", "glas", "dodgeColorTest"])
+def test_product_boundingbox_splitter_matches_reference(hostsim, rtp, model):
+    m = load_golden_mesh(model)
+    s = HostSimScene(hostsim, rtp, m, with_boxes=False)  # boxes built by csrc/ref_boxes.cpp
+    bb, off, bf = s.boxes()
+    s.close()
+    assert bb.shape == m.boxes.shape and np.array_equal(bb.view(np.int32), m.boxes.view(np.int32))
+    assert np.array_equal(off, m.box_off) and np.array_equal(bf, m.box_faces)
+
+
+def test_caller_supplied_boxes_restrict_visibility(hostsim, rtp, po):
+    """Faces missing from the BoundingBox list are invisible, as in flyscene.cpp:381-393."""
+    m = load_golden_mesh("cube")
+    keep = m.box_faces[::2].copy()
+    m2 = po.Mesh(m.verts, m.normals, m.faces, m.face_mat, m.materials, None, m.shape)
+    m2.set_boxes(m.boxes, np.array([0, len(keep)], np.int32), keep)
+    s = HostSimScene(hostsim, rtp, m2, with_boxes=True)
+    a = s.render(48, 48, None, 2, None, None)
+    s.close()
+    b = po.render(m2, 48, 48)
+    assert np.array_equal(a["hit"], b["hit"]) and bits_equal(a["rgb"], b["rgb"]).all()
+    assert set(np.unique(a["hit"])) <= set(keep.tolist()) | {-1}
+
+
+def test_ray_batches_match_oracle(hostsim, rtp, po):
+    m = load_golden_mesh("dodgeColorTest")
+    rng = np.random.default_rng(7)
+    n = 3000
+    o = rng.uniform(-1.2, 1.2, (n, 3)).astype(np.float32)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True).astype(np.float32)
+    d[:50, 0] = 0.0  # axis-parallel directions: inf / NaN slabs in the reference box test (Q13)
+    d[50:100, 1] = 0.0
+    d[100:120, :2] = 0.0
+    rays = np.concatenate([o, d], 1)
+    s = HostSimScene(hostsim, rtp, m)
+    face, t = s.rays(rays, anyhit=False)
+    occ, _ = s.rays(rays, anyhit=True)
+    s.close()
+    f2, t2 = po.closest_rays(m, rays, threads=4)
+    assert np.array_equal(face, f2) and bits_equal(t, t2).all()
+    assert np.array_equal(occ, po.shadow_rays(m, rays, threads=4))
+    assert (face >= 0).sum() > 100
+
+
+def test_tile_tables_partition_the_image(hostsim):
+    import ctypes as C
+    for (w, h, world) in [(64, 64, 1), (100, 70, 2), (1920, 1080, 8), (33, 31, 4)]:
+        tx, ty = (w + 31) // 32, (h + 31) // 32
+        seen = np.zeros(tx * ty, np.int32)
+        for r in range(world):
+            tiles, loc, n = np.zeros(tx * ty, np.int32), np.zeros(tx * ty, np.int32), C.c_int()
+            hostsim.hostsim_tile_tables(w, h, r, world, tiles.ctypes.data_as(C.c_void_p), C.byref(n),
+                                        loc.ctypes.data_as(C.c_void_p))
+            own = tiles[:n.value]
+            seen[own] += 1
+            assert np.array_equal(loc[own], np.arange(n.value))
+            assert abs(n.value - tx * ty / world) <= max(tx, ty)
+        assert (seen == 1).all()
