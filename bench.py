@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py - Mrays/s of the ray-tracing hot path on N B200s, with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c3] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One step = one full frame of the workload traced through the wavefront kernels
+(primary + shadow + reflection rays), from camera/light parameters to the quantised 8-bit
+image on GPU 0.  `value` is device-timed (CUDA events) with the scene resident in HBM; `e2e` is
+the same frame through the public C ABI call rtp_render() with HOST output buffers (camera and
+lights uploaded, image downloaded inside the timed region).  With N > 1 the image is split into
+interleaved 32x32 screen tiles (strong scaling: total work fixed), the scene is replicated, and
+tiles are gathered to GPU 0 with one NCCL gather per frame.
+
+Workloads (BASELINE.json configs; --workload):
+  c3 (default) synthetic terrain, 1 002 528 triangles, 1920x1080, 1 light, max_depth 1
+               (primary + shadow rays) - the config the >= 1 Grays/s-per-B200 target is quoted on
+  c2           shipped default scene (dodgeColorTest, 16 311 triangles), 1920x1080, 4 lights,
+               max_depth 4 (reflection depth 3)
+  c1           plane.obj, 256x256, 1 light, max_depth 2
+"""
+import argparse
+import importlib
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+METRIC = "Mrays/sec (primary+secondary)"
+UNIT = "Mrays/s"
+
+
+def b_alg(n_tris):
+    """algorithmic bytes per ray for a BVH2 with 64-B nodes and <= 4-triangle
+    leaves of 48 B/triangle: one root-to-leaf descent, one leaf, one 16-B hit record."""
+    return 64 * math.ceil(math.log2(max(n_tris / 4.0, 2.0))) + 4 * 48 + 16
+
+
+def load_golden_mesh(name):
+    z = np.load(os.path.join(ROOT, "tests", "golden", f"mesh_{name}.npz"))
+    return {k: z[k] for k in ("verts", "normals", "faces", "face_mat", "materials", "shape")}
+
+
+def build_workload(name, synth):
+    if name == "c3":
+        m = synth.terrain(708)
+        return dict(mesh=m, w=1920, h=1080, max_depth=1, lights=synth.LIGHT_DEFAULT,
+                    view=synth.look_at((0.0, 0.30, 0.20), (0.0, -0.05, -0.08)),
+                    desc="C3: synthetic fBm terrain 708x708 cells = 1002528 triangles, 1920x1080, 1 point light, "
+                         "max_depth 1 (primary+shadow), camera eye (0,.30,.20) -> (0,-.05,-.08), ~93% coverage")
+    if name == "c2":
+        m = load_golden_mesh("dodgeColorTest")
+        c = np.load(os.path.join(ROOT, "tests", "golden", "case_dodge_c2.npz"))
+        return dict(mesh=m, w=1920, h=1080, max_depth=4, lights=synth.LIGHTS_C2, view=c["view"],
+                    desc="C2: dodgeColorTest.obj (16311 triangles), 1920x1080, 4 point lights, max_depth 4")
+    if name == "c1":
+        m = load_golden_mesh("plane")
+        return dict(mesh=m, w=256, h=256, max_depth=2, lights=synth.LIGHT_DEFAULT, view=None,
+                    desc="C1: plane.obj (2 triangles), 256x256, 1 point light, max_depth 2, default camera")
+    raise SystemExit(f"unknown workload {name}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                pass
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=reasons, samples=len(sm))
+
+
+def cpu_baseline_port(wl, n_rays_target=None, seconds=15.0):
+    """The oracle (plain-C port of the reference path, all host threads) on a bounded pixel
+    subsample of the same frame.  Reported baseline only."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    m = wl["mesh"]
+    t0 = time.perf_counter()
+    mesh = po.Mesh(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], None, m["shape"]).build_boxes()
+    t_boxes = time.perf_counter() - t0
+    cores = os.cpu_count() or 1
+    w, h = wl["w"], wl["h"]
+    rng = np.random.default_rng(1234)
+
+    def sample(n):
+        idx = rng.choice(w * h, size=min(n, w * h), replace=False)
+        return np.stack([idx % w, idx // w], 1).astype(np.int32)
+    px = sample(64 * cores)  # calibration
+    t0 = time.perf_counter()
+    o = po.render(mesh, w, h, view=wl["view"], max_depth=wl["max_depth"], point_lights=wl["lights"], pixels=px, threads=cores)
+    dt = max(time.perf_counter() - t0, 1e-6)
+    n = int(min(w * h, max(len(px), len(px) * seconds / dt)))
+    px = sample(n)
+    t0 = time.perf_counter()
+    o = po.render(mesh, w, h, view=wl["view"], max_depth=wl["max_depth"], point_lights=wl["lights"], pixels=px, threads=cores)
+    dt = time.perf_counter() - t0
+    rays = sum(o["counts"][k] for k in ("primary", "shadow", "reflection"))
+    return dict(value=rays / dt / 1e6, unit=UNIT, cores=cores, kind="port",
+                sample=f"{len(px)} random pixels of the {w}x{h} frame ({rays} rays) in {dt:.2f} s, oracle/oracle.c "
+                       f"with {cores} pthreads; BoundingBox build {t_boxes:.1f} s untimed")
+
+
+def run_reference(args, wl, synth):
+    """--impl reference: the reference's own CPU implementation (oracle/_ref/ref_harness = the
+    unmodified flyscene.cpp + BoundingBox.cpp) on all host cores, bounded pixel sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+    cores = os.cpu_count() or 1
+    w, h = wl["w"], wl["h"]
+    rng = np.random.default_rng(1234)
+    reps = args.steps + args.warmup
+    if po.ref_available():
+        import tempfile
+        tmp = tempfile.mkdtemp(prefix="rtp_bench_ref_")
+        obj = synth.write_obj(wl["mesh"], os.path.join(tmp, "workload.obj"))
+        # calibrate on a tiny sample, then size the per-step sample for ~60 s total
+        def run(n, repeat):
+            idx = rng.choice(w * h, size=min(n, w * h), replace=False)
+            px = np.stack([idx % w, idx // w], 1).astype(np.int32)
+            return po.ref_run(obj, w, h, view=wl["view"], max_depth=wl["max_depth"], point_lights=wl["lights"],
+                              pixels=px, procs=cores, repeat=repeat, chain=True)
+        r = run(8 * cores, 1)
+        per_px = max(r["pass_seconds"][-1], 1e-6) / (8 * cores)
+        n = int(min(w * h, max(8 * cores, 60.0 / reps / per_px)))
+        r = run(n, reps)
+        rays = sum(r["counts"][k] for k in ("primary", "shadow", "reflection"))
+        times = r["pass_seconds"][args.warmup:]
+        kind, what = "reference", "oracle/_ref/ref_harness (reference flyscene.cpp + BoundingBox.cpp, -O2)"
+    else:
+        m = wl["mesh"]
+        mesh = po.Mesh(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], None, m["shape"]).build_boxes()
+        idx = rng.choice(w * h, size=min(64 * cores, w * h), replace=False)
+        px = np.stack([idx % w, idx // w], 1).astype(np.int32)
+        t0 = time.perf_counter()
+        po.render(mesh, w, h, view=wl["view"], max_depth=wl["max_depth"], point_lights=wl["lights"], pixels=px, threads=cores)
+        per_px = max(time.perf_counter() - t0, 1e-6) / len(px)
+        n = int(min(w * h, max(len(px), 60.0 / reps / per_px)))
+        idx = rng.choice(w * h, size=n, replace=False)
+        px = np.stack([idx % w, idx // w], 1).astype(np.int32)
+        times = []
+        for it in range(reps):
+            t0 = time.perf_counter()
+            o = po.render(mesh, w, h, view=wl["view"], max_depth=wl["max_depth"], point_lights=wl["lights"], pixels=px, threads=cores)
+            if it >= args.warmup:
+                times.append(time.perf_counter() - t0)
+        rays = sum(o["counts"][k] for k in ("primary", "shadow", "reflection"))
+        kind, what = "port", "oracle/oracle.c (reference binary not present on this box)"
+    total = sum(times)
+    value = rays * len(times) / total / 1e6
+    sample = f"{n} random pixels of the {w}x{h} frame per step ({rays} rays), {what}, {cores} processes/threads"
+    line = dict(impl="reference", metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=1e3 * total / len(times), higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=wl["desc"], impl="reference CPU path on host cores"),
+                cpu_baseline=dict(value=value, unit=UNIT, cores=cores, kind=kind, sample=sample),
+                e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+def run_ours(args, wl, rtp):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the hot path is CUDA only (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    m, w, h, md = wl["mesh"], wl["w"], wl["h"], wl["max_depth"]
+    t0 = time.perf_counter()
+    scene = rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], device=local)
+    t_build = time.perf_counter() - t0
+    scene.set_lights(wl["lights"], None)
+    scene.set_camera(w, h, wl["view"])
+    info = scene.info()
+    stride = rtp.tile_buffer_bytes(w, h, rank, world)
+    tiles = torch.zeros(stride // 4, dtype=torch.float32, device=dev)
+    gathered = torch.zeros(world * stride // 4, dtype=torch.float32, device=dev) if (world > 1 and rank == 0) else None
+    rgb8 = torch.zeros(w * h * 3, dtype=torch.uint8, device=dev) if rank == 0 else None
+    rgb8_host = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory() if rank == 0 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step(profile=False):
+        scene.render_tiles_device(w, h, tiles.data_ptr(), max_depth=md, rank=rank, world=world, stream=stream,
+                                  flags=rtp.RENDER_PROFILE if profile else 0)
+        if world > 1:
+            dist.gather(tiles, list(gathered.chunk(world)) if rank == 0 else None, dst=0)
+        if rank == 0:
+            src = gathered if world > 1 else tiles
+            scene.untile_device(w, h, world, src.data_ptr(), stride, d_rgb8=rgb8.data_ptr(), stream=stream)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+    st = scene.frame_stats()
+    counts = torch.tensor([st["rays_primary"], st["rays_shadow"], st["rays_reflection"], st["hits"]],
+                          dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(counts)
+    rays_frame = int(counts[:3].sum().item())
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms_steps, k_closest, k_shade = [], [], []
+    for _ in range(args.steps):
+        flush.zero_()          # evict the scene from L2 between timed iterations (untimed)
+        sync_all()
+        ev0.record()
+        step(profile=True)     # per-kernel CUDA events are recorded on the launch stream, read after the sync
+        ev1.record()
+        sync_all()
+        t = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_steps.append(float(t.item()))
+        fs = scene.frame_stats()
+        k_closest.append(fs["ms_closest"])
+        k_shade.append(fs["ms_anyhit"])
+    clocks = sampler.stop() if rank == 0 else None
+    launches_rank0 = (2 * md + 1 + 1) * args.steps
+
+    # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
+    e2e_ms = []
+    cam_bytes = 4 * (12 + 4 + 2) + 24 * len(wl["lights"])
+    for it in range(args.steps + 1):
+        sync_all()
+        t0 = time.perf_counter()
+        scene.set_lights(wl["lights"], None)
+        scene.set_camera(w, h, wl["view"])
+        if world == 1:
+            scene.render(w, h, max_depth=md, want=("rgb8",), out={"rgb8": rgb8_host.numpy().reshape(h, w, 3)})
+        else:
+            step()
+            if rank == 0:
+                rgb8_host.copy_(rgb8, non_blocking=True)
+        sync_all()
+        if it > 0:
+            t = torch.tensor([1e3 * (time.perf_counter() - t0)], device=dev)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms.append(float(t.item()))
+
+    if rank == 0:
+        total_ms = sum(ms_steps)
+        value = rays_frame * args.steps / (total_ms / 1e3) / 1e6
+        e2e_val = rays_frame * len(e2e_ms) / (sum(e2e_ms) / 1e3) / 1e6
+        # roofline of the dominant kernel (rank 0's launches; algorithmic bytes from SURVEY.md 8d)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        n_tris = info["n_triangles"]
+        mc, ms_ = float(np.mean(k_closest)), float(np.mean(k_shade))
+        own = float(st["rays_primary"] + st["rays_reflection"]), float(st["rays_shadow"])
+        dom = "k_closest" if mc >= ms_ else "k_shade"
+        dom_ms, dom_rays = (mc, own[0]) if mc >= ms_ else (ms_, own[1])
+        achieved = dom_rays * b_alg(n_tris) / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dom)
+        except Exception:
+            pass
+        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                    ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
+                    dtype="f32", data="synthetic",
+                    config=dict(workload=wl["desc"], rays_per_frame=rays_frame, triangles=n_tris, bvh_nodes=info["n_bvh_nodes"],
+                                parallelism=f"tile{world}" if world > 1 else "1gpu",
+                                l2="256 MiB memset between timed steps (untimed) flushes the 126 MB L2",
+                                scene_build_s=round(t_build, 2)),
+                    clocks=clocks,
+                    e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=cam_bytes, d2h_bytes_per_step=w * h * 3,
+                             ms_per_step=float(np.mean(e2e_ms)),
+                             what="rtp_set_lights + rtp_set_camera + rtp_render -> host uint8 image" if world == 1 else
+                                  "set lights/camera + tile render + NCCL gather + untile + D2H of the uint8 image on rank 0"),
+                    gpu_launches=launches_rank0,
+                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
+                                  traffic=traffic, kernel=dom, kernel_ms=dom_ms, rays_per_launch_set=dom_rays,
+                                  alg_bytes_per_ray=b_alg(n_tris),
+                                  peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
+                                  kernels_ms=dict(k_closest=mc, k_shade=ms_)))
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_port(wl)
+        print(json.dumps(line))
+    scene.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rtp = importlib.import_module("ray-tracing-project_b200")
+    synth = importlib.import_module("ray-tracing-project_b200.synth")
+    wl = build_workload(args.workload, synth)
+    if args.impl == "reference":
+        run_reference(args, wl, synth)
+    else:
+        run_ours(args, wl, rtp)
+
+
+if __name__ == "__main__":
+    main()

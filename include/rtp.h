@@ -85,6 +85,7 @@ typedef struct rtp_render_opts {
   int32_t flags;         /* RTP_RENDER_* */
 } rtp_render_opts;
 #define RTP_RENDER_DEFAULT 0
+#define RTP_RENDER_PROFILE 1 /* bracket each trace kernel with CUDA events -> ms_closest / ms_anyhit */
 
 typedef struct rtp_stats {
   int64_t rays_primary, rays_shadow, rays_reflection, hits;
@@ -92,7 +93,8 @@ typedef struct rtp_stats {
   float ms_total;       /* device time incl. output conversion, excl. H2D/D2H              */
   int32_t kernel_launches;
   int32_t n_bvh_nodes, n_triangles;
-  float ms_closest, ms_anyhit; /* summed device time of the two traversal kernels           */
+  float ms_closest, ms_anyhit; /* with RTP_RENDER_PROFILE: summed device time of the closest-hit
+                                  kernels and of the shadow(any-hit)+shade kernels             */
 } rtp_stats;
 
 /* ---- lifetime ---------------------------------------------------------------------------- */
@@ -150,6 +152,9 @@ int rtp_scene_box_count(const rtp_scene *s);
 int rtp_scene_get_boxes(const rtp_scene *s, float *boxes /* B x 6 */, int32_t *box_off /* B+1 */,
                         int32_t *box_faces /* F */);
 int rtp_scene_info(const rtp_scene *s, rtp_stats *st);
+/* Waits for the most recently enqueued frame (rtp_render_tiles_device / rtp_render) and returns
+ * its ray counters and, if it ran with RTP_RENDER_PROFILE, the per-kernel device times. */
+int rtp_frame_stats(rtp_scene *s, rtp_stats *st);
 const char *rtp_last_error(void);
 int rtp_abi_version(void);
 

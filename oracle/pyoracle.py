@@ -226,14 +226,15 @@ def ref_model(name):
 
 def ref_run(obj, w, h, view=None, fovy=60.0, point_lights=None, dir_lights=None, max_depth=2,
             pixels=None, stride=None, procs=1, dump_scene=False, chain=True, mode="render", rays=None,
-            keep_dir=None):
+            keep_dir=None, repeat=1):
     """Run the reference binary. Returns dict of numpy arrays (+ 'mesh' when dump_scene)."""
     if not ref_available():
         raise RuntimeError("oracle/_ref/ref_harness not built (run `make -C oracle ref` where /root/reference exists)")
     tmp = keep_dir or tempfile.mkdtemp(prefix="rtp_ref_")
     pre = os.path.join(tmp, "o")
     lines = [f"obj {os.path.abspath(obj)}", f"out {pre}", f"size {w} {h}", f"fovy {fovy!r}", f"max_depth {max_depth}",
-             f"procs {procs}", f"dump_scene {int(dump_scene)}", f"chain {int(chain)}", f"mode {mode}"]
+             f"procs {procs}", f"dump_scene {int(dump_scene)}", f"chain {int(chain)}", f"mode {mode}",
+             f"repeat {repeat}"]
     if view is not None:
         lines.append("view " + " ".join(repr(float(x)) for x in _f32(view, (12,))))
     if point_lights is not None or dir_lights is not None:
@@ -270,6 +271,7 @@ def ref_run(obj, w, h, view=None, fovy=60.0, point_lights=None, dir_lights=None,
         tt = open(pre + ".time.txt").read().split()
         out["trace_seconds"], out["wall_seconds"] = float(tt[0]), float(tt[1])
         out["counts"] = dict(primary=int(tt[4]), shadow=int(tt[5]), reflection=int(tt[6]), hits=int(tt[7]))
+        out["pass_seconds"] = [float(x) for x in tt[8:]]
     else:
         tt = open(pre + ".time.txt").read().split()
         out["trace_seconds"] = float(tt[0])

@@ -48,6 +48,7 @@ struct Job {
   int procs = 1;
   bool dump_scene = false;
   bool chain = true;        // also walk the hit chain for hit index / ray counts
+  int repeat = 1;           // timed passes over the pixel list (bench: warm-up + steps)
 };
 
 bool parse_job(const char* path, Job& j) {
@@ -74,6 +75,7 @@ bool parse_job(const char* path, Job& j) {
     else if (k == "procs") s >> j.procs;
     else if (k == "dump_scene") { int v; s >> v; j.dump_scene = v != 0; }
     else if (k == "chain") { int v; s >> v; j.chain = v != 0; }
+    else if (k == "repeat") s >> j.repeat;
     else { fprintf(stderr, "ref_harness: unknown key '%s'\n", k.c_str()); return false; }
   }
   return !j.obj.empty() && !j.out.empty();
@@ -292,7 +294,8 @@ int main(int argc, char** argv) {
   float* tprim = shared_alloc<float>(n);
   int* hit = shared_alloc<int>(n);
   long long* counts = shared_alloc<long long>(size_t(job.procs) * 4);  // primary, shadow, reflection, hits
-  double* tsec = shared_alloc<double>(job.procs);
+  if (job.repeat < 1) job.repeat = 1;
+  double* tsec = shared_alloc<double>(size_t(job.procs) * job.repeat);
 
   auto t0 = std::chrono::steady_clock::now();
   std::vector<pid_t> kids;
@@ -300,17 +303,19 @@ int main(int argc, char** argv) {
     pid_t pid = job.procs > 1 ? fork() : 0;
     if (pid == 0) {
       // timed part: exactly the body of traceRayThread (flyscene.cpp:301-310)
-      auto c0 = std::chrono::steady_clock::now();
       Eigen::Vector3f origin = fs.flycamera.getCenter();
       Eigen::Vector3f direction;
-      // interleave rows of the pixel list over processes (row bands would be unbalanced)
-      for (size_t k = p; k < n; k += job.procs) {
-        int i = px[2 * k], j = px[2 * k + 1];
-        direction = (fs.flycamera.screenToWorld(Eigen::Vector2f(i, j)) - origin).normalized();
-        Eigen::Vector3f c = fs.traceRay(origin, direction, 0, false);
-        for (int ch = 0; ch < 3; ++ch) { rgb[k * 3 + ch] = c(ch); dirs[k * 3 + ch] = direction(ch); }
+      for (int rep = 0; rep < job.repeat; ++rep) {
+        auto c0 = std::chrono::steady_clock::now();
+        // interleave the pixel list over processes (row bands would be unbalanced)
+        for (size_t k = p; k < n; k += job.procs) {
+          int i = px[2 * k], j = px[2 * k + 1];
+          direction = (fs.flycamera.screenToWorld(Eigen::Vector2f(i, j)) - origin).normalized();
+          Eigen::Vector3f c = fs.traceRay(origin, direction, 0, false);
+          for (int ch = 0; ch < 3; ++ch) { rgb[k * 3 + ch] = c(ch); dirs[k * 3 + ch] = direction(ch); }
+        }
+        tsec[size_t(p) * job.repeat + rep] = std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();
       }
-      tsec[p] = std::chrono::duration<double>(std::chrono::steady_clock::now() - c0).count();
       // untimed part: walk the hit chain for the primary face index and the ray counts
       long long np = 0, ns = 0, nr = 0, nh = 0;
       if (job.chain) {
@@ -346,10 +351,13 @@ int main(int argc, char** argv) {
   double wall = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   double tmax = 0;
   long long tot[4] = {0, 0, 0, 0};
+  std::vector<double> trep(job.repeat, 0.0);  // per pass: max over processes
   for (int p = 0; p < job.procs; ++p) {
-    tmax = std::max(tmax, tsec[p]);
+    for (int rep = 0; rep < job.repeat; ++rep)
+      trep[rep] = std::max(trep[rep], tsec[size_t(p) * job.repeat + rep]);
     for (int c = 0; c < 4; ++c) tot[c] += counts[p * 4 + c];
   }
+  tmax = trep[job.repeat - 1];
   write_bin(job.out + ".rgb.f32", rgb, n * 3);
   write_bin(job.out + ".dir.f32", dirs, n * 3);
   write_bin(job.out + ".pixels.i32", px.data(), px.size());
@@ -359,7 +367,9 @@ int main(int argc, char** argv) {
   }
   FILE* f = fopen((job.out + ".time.txt").c_str(), "w");
   // trace seconds (max over processes), wall seconds incl. chain walk, pixels, procs, rays p/s/r, hits
-  fprintf(f, "%.9f %.9f %zu %d %lld %lld %lld %lld\n", tmax, wall, n, job.procs, tot[0], tot[1], tot[2], tot[3]);
+  fprintf(f, "%.9f %.9f %zu %d %lld %lld %lld %lld", tmax, wall, n, job.procs, tot[0], tot[1], tot[2], tot[3]);
+  for (double t : trep) fprintf(f, " %.9f", t);
+  fprintf(f, "\n");
   fclose(f);
   if (system(rmcmd.c_str())) {}
   return 0;

@@ -61,7 +61,7 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version"]
+           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats"]
 
 _lib = None
 
@@ -98,6 +98,7 @@ def lib():
         L.rtp_scene_box_count.argtypes = [C.c_void_p]
         L.rtp_scene_get_boxes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rtp_scene_info.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
+        L.rtp_frame_stats.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
         _lib = L
     return _lib
 
@@ -158,9 +159,12 @@ def make_lights_struct(point=None, dirl=None):
     return l, [point, dirl]
 
 
-def make_opts(w, h, max_depth=2, background=BACKGROUND, rank=0, world=1):
+RENDER_PROFILE = 1
+
+
+def make_opts(w, h, max_depth=2, background=BACKGROUND, rank=0, world=1, flags=0):
     o = RtpRenderOpts()
-    o.width, o.height, o.max_depth, o.rank, o.world, o.flags = w, h, max_depth, rank, world, 0
+    o.width, o.height, o.max_depth, o.rank, o.world, o.flags = w, h, max_depth, rank, world, flags
     o.background = (C.c_float * 3)(*_f32(background, (3,)).tolist())
     return o
 
@@ -206,6 +210,12 @@ class Scene:
         self._check(self._L.rtp_scene_info(self._h, C.byref(st)))
         return st.as_dict()
 
+    def frame_stats(self):
+        """Waits for the last enqueued frame; ray counters (+ per-kernel ms with RENDER_PROFILE)."""
+        st = RtpStats()
+        self._check(self._L.rtp_frame_stats(self._h, C.byref(st)))
+        return st.as_dict()
+
     def boxes(self):
         n = self._L.rtp_scene_box_count(self._h)
         b = np.zeros((n, 6), np.float32)
@@ -214,9 +224,10 @@ class Scene:
         self._check(self._L.rtp_scene_get_boxes(self._h, b.ctypes.data, off.ctypes.data, bf.ctypes.data))
         return b, off, bf[:off[-1]]
 
-    def render(self, w, h, max_depth=2, background=BACKGROUND, want=("rgb", "hit"), rank=0, world=1, out=None):
+    def render(self, w, h, max_depth=2, background=BACKGROUND, want=("rgb", "hit"), rank=0, world=1, out=None,
+               flags=0):
         """rtp_render into host arrays. Returns dict(rgb, rgb8, hit, stats)."""
-        o = make_opts(w, h, max_depth, background, rank, world)
+        o = make_opts(w, h, max_depth, background, rank, world, flags)
         out = dict(out or {})
         if "rgb" in want and "rgb" not in out:
             out["rgb"] = np.zeros((h, w, 3), np.float32)
@@ -231,8 +242,8 @@ class Scene:
         return out
 
     def render_tiles_device(self, w, h, d_tiles_ptr, max_depth=2, background=BACKGROUND, rank=0, world=1,
-                            stream=None, want_stats=False):
-        o = make_opts(w, h, max_depth, background, rank, world)
+                            stream=None, want_stats=False, flags=0):
+        o = make_opts(w, h, max_depth, background, rank, world, flags)
         st = RtpStats()
         self._check(self._L.rtp_render_tiles_device(self._h, C.byref(o), d_tiles_ptr, stream,
                                                     C.byref(st) if want_stats else None))

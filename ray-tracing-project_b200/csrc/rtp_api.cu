@@ -81,6 +81,10 @@ struct rtp_scene {
   LaunchCfg cfg;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
+  int kev_used = 0;
+  cudaStream_t last_stream = nullptr;  // stream of the most recently enqueued frame
+  int last_launches = 0;
   Frame frame;   // pixel frames (camera rays)
   Frame rframe;  // ray-batch frames (rtp_trace_rays SHADE)
   DevBuf<float> rays_dev;
@@ -176,6 +180,7 @@ int rtp_scene_destroy(rtp_scene *s) {
   if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
   for (auto &ev : s->ev)
     if (ev) cudaEventDestroy(ev);
+  for (auto &ev : s->kev) cudaEventDestroy(ev);
   delete s;  // DevBuf destructors free device memory while the device is current
   return RTP_OK;
 }
@@ -280,18 +285,31 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
 }
 
 // Enqueues one frame: 2 * max_depth trace kernels + resolve.  Returns the number of launches.
-int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches) {
+// profile: bracket every trace kernel with CUDA events (summed later by kernel_times).
+int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile = false) {
   CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), st));
   CK(cudaMemsetAsync(s->stats.p, 0, kStatCount * sizeof(unsigned long long), st));
   int n = 0;
+  s->kev_used = 0;
+  if (profile)
+    while ((int)s->kev.size() < 3 * p.max_depth + 1) {
+      cudaEvent_t e;
+      CK(cudaEventCreate(&e));
+      s->kev.push_back(e);
+    }
   for (int d = 0; d < p.max_depth; ++d) {
+    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
     launch_closest(p, d, s->cfg, st);
+    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
     launch_shade(p, d, s->cfg, st);
+    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
     n += 2;
   }
   launch_resolve(p, st);
   ++n;
   CK(cudaGetLastError());
+  s->last_stream = st;
+  s->last_launches = n;
   if (launches) *launches = n;
   return RTP_OK;
 }
@@ -311,6 +329,13 @@ int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
   unsigned long long h[kStatCount];
   CK(cudaMemcpyAsync(h, s->stats.p, sizeof h, cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
+  for (int i = 0; i + 2 < s->kev_used; i += 3) {  // (before closest, between, after shade) per depth
+    float a = 0.f, b = 0.f;
+    CK(cudaEventElapsedTime(&a, s->kev[i], s->kev[i + 1]));
+    CK(cudaEventElapsedTime(&b, s->kev[i + 1], s->kev[i + 2]));
+    st->ms_closest += a;
+    st->ms_anyhit += b;
+  }
   st->rays_primary = (int64_t)h[kStatPrimary];
   st->rays_shadow = (int64_t)h[kStatShadow];
   st->rays_reflection = (int64_t)h[kStatReflection];
@@ -323,6 +348,16 @@ int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
 }  // namespace
 
 extern "C" {
+
+int rtp_frame_stats(rtp_scene *s, rtp_stats *st) {
+  if (!s || !st) return fail(RTP_ERR_INVALID, "rtp_frame_stats: null argument");
+  DeviceGuard g(s->device);
+  std::memset(st, 0, sizeof *st);
+  int rc = read_stats(s, st, s->last_stream ? s->last_stream : s->stream);
+  if (rc) return rc;
+  st->kernel_launches = s->last_launches;
+  return RTP_OK;
+}
 
 size_t rtp_tile_buffer_bytes(int width, int height, int rank, int world) {
   if (width <= 0 || height <= 0 || world < 1) return 0;
@@ -344,7 +379,7 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   fill_params(s, s->frame, *o, (float4 *)d_tiles, p);
   int launches = 0;
   if (st) CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches);
+  rc = enqueue_frame(s, p, cs, &launches, st && (o->flags & RTP_RENDER_PROFILE));
   if (rc) return rc;
   if (st) {
     CK(cudaEventRecord(s->ev[1], cs));
@@ -391,7 +426,7 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   fill_params(s, f, *o, f.fb.p, p);
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches);
+  rc = enqueue_frame(s, p, cs, &launches, st && (o->flags & RTP_RENDER_PROFILE));
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
   if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
