@@ -86,19 +86,23 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([time.perf_counter()] + [x.strip() for x in line.split(",")])
 
-    def stop(self):
+    def stop(self, t_begin=None, t_end=None):
         if self.proc:
             self.proc.terminate()
             try:
                 self.proc.wait(timeout=5)
             except Exception:
                 pass
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        rows = [r[1:] for r in self.rows if len(r) >= 7 and (t_begin is None or t_begin <= r[0] <= t_end)]
+        if not rows:  # region shorter than one sampling period: fall back to everything we saw
+            rows = [r[1:] for r in self.rows if len(r) >= 7]
+        num = lambda x: x.replace(".", "", 1).isdigit()
+        sm = [float(r[0]) for r in rows if num(r[0])]
+        mx = [float(r[1]) for r in rows if num(r[1])]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        reasons = sorted({names[i] for r in rows for i in range(4) if r[2 + i].lower() == "active"})
         return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
                     reasons=reasons, samples=len(sm))
 
@@ -235,6 +239,9 @@ def run_ours(args, wl, rtp):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(args.warmup, 3)):
         step()
     sync_all()
@@ -245,9 +252,7 @@ def run_ours(args, wl, rtp):
         dist.all_reduce(counts)
     rays_frame = int(counts[:3].sum().item())
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    t_begin = time.perf_counter()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ms_steps, k_closest, k_shade = [], [], []
     for _ in range(args.steps):
@@ -264,7 +269,7 @@ def run_ours(args, wl, rtp):
         fs = scene.frame_stats()
         k_closest.append(fs["ms_closest"])
         k_shade.append(fs["ms_anyhit"])
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
     launches_rank0 = (2 * md + 1 + 1) * args.steps
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
@@ -339,8 +344,8 @@ def run_ours(args, wl, rtp):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -84,6 +84,7 @@ struct rtp_scene {
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
   int kev_used = 0;
   cudaStream_t last_stream = nullptr;  // stream of the most recently enqueued frame
+  bool has_last = false;
   int last_launches = 0;
   Frame frame;   // pixel frames (camera rays)
   Frame rframe;  // ray-batch frames (rtp_trace_rays SHADE)
@@ -287,6 +288,8 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
 // Enqueues one frame: 2 * max_depth trace kernels + resolve.  Returns the number of launches.
 // profile: bracket every trace kernel with CUDA events (summed later by kernel_times).
 int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile = false) {
+  // one frame at a time per scene: counters and path buffers are shared between frames
+  if (s->has_last && s->last_stream != st) CK(cudaStreamSynchronize(s->last_stream));
   CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), st));
   CK(cudaMemsetAsync(s->stats.p, 0, kStatCount * sizeof(unsigned long long), st));
   int n = 0;
@@ -309,6 +312,7 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   ++n;
   CK(cudaGetLastError());
   s->last_stream = st;
+  s->has_last = true;
   s->last_launches = n;
   if (launches) *launches = n;
   return RTP_OK;
@@ -353,7 +357,7 @@ int rtp_frame_stats(rtp_scene *s, rtp_stats *st) {
   if (!s || !st) return fail(RTP_ERR_INVALID, "rtp_frame_stats: null argument");
   DeviceGuard g(s->device);
   std::memset(st, 0, sizeof *st);
-  int rc = read_stats(s, st, s->last_stream ? s->last_stream : s->stream);
+  int rc = read_stats(s, st, s->has_last ? s->last_stream : s->stream);
   if (rc) return rc;
   st->kernel_launches = s->last_launches;
   return RTP_OK;
@@ -371,7 +375,7 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   if (rc) return rc;
   if (!d_tiles) return fail(RTP_ERR_INVALID, "rtp_render_tiles_device: null tile buffer");
   DeviceGuard g(s->device);
-  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  cudaStream_t cs = (cudaStream_t)stream;  // NULL = the legacy default stream, as documented
   const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
   rc = ensure_frame(s, s->frame, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
   if (rc) return rc;
@@ -379,7 +383,7 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   fill_params(s, s->frame, *o, (float4 *)d_tiles, p);
   int launches = 0;
   if (st) CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, st && (o->flags & RTP_RENDER_PROFILE));
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0);
   if (rc) return rc;
   if (st) {
     CK(cudaEventRecord(s->ev[1], cs));
@@ -398,7 +402,7 @@ int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void
   if (!s || !d_all || width <= 0 || height <= 0 || world < 1) return fail(RTP_ERR_INVALID, "rtp_untile_device: bad argument");
   if (rank_stride_bytes % sizeof(float4)) return fail(RTP_ERR_INVALID, "rtp_untile_device: stride must be a multiple of 16");
   DeviceGuard g(s->device);
-  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  cudaStream_t cs = (cudaStream_t)stream;
   Frame &f = s->frame;
   if (f.width != width || f.height != height || f.world != world || !f.local_of_tile.p)
     return fail(RTP_ERR_STATE, "rtp_untile_device: render a frame of this size/world first");
@@ -426,7 +430,7 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   fill_params(s, f, *o, f.fb.p, p);
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, st && (o->flags & RTP_RENDER_PROFILE));
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
   if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
@@ -460,7 +464,7 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
                           void *d_occluded, void *stream, rtp_stats *st) {
   if (!s || !d_rays || n < 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: bad argument");
   DeviceGuard g(s->device);
-  cudaStream_t cs = stream ? (cudaStream_t)stream : s->stream;
+  cudaStream_t cs = (cudaStream_t)stream;
   int *cursor = s->counters.p + kCtrAux;
   CK(cudaMemsetAsync(cursor, 0, sizeof(int), cs));
   if (st) CK(cudaEventRecord(s->ev[0], cs));

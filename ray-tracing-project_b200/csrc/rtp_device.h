@@ -148,70 +148,112 @@ RTP_HD bool tri_exact(const DeviceScene &S, int slot, v3 o, v3 d, float tmax, fl
 // ANY = true : shadow (flyscene.cpp:510-526): any such face.
 // o/d: origin and direction used for the face tests; bo: origin used for the reference box test
 // (== o for closest-hit, the un-offset point P for shadow rays).
-template <bool ANY>
-RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int &best_slot) {
+//
+// The traversal is resumable (Trav + trav_step) so that the persistent-warp kernels can refill
+// idle lanes with new rays between steps; traverse<> is the plain run-to-completion loop.
+struct Trav {
+  float idx, idy, idz, oodx, oody, oodz;
+  v3 o, d;
+  int node, sp;
+  float tbest;
+  unsigned rbest;
+  int sbest;
+};
+
+RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
   const float ooeps = 1.0e-24f;
   float dx = fabsf(d.x) > ooeps ? d.x : copysignf(ooeps, d.x);
   float dy = fabsf(d.y) > ooeps ? d.y : copysignf(ooeps, d.y);
   float dz = fabsf(d.z) > ooeps ? d.z : copysignf(ooeps, d.z);
-  const float idx = 1.0f / dx, idy = 1.0f / dy, idz = 1.0f / dz;
-  const float oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
-  int stack[kStackSize];
-  int sp = 0;
+  t.idx = 1.0f / dx; t.idy = 1.0f / dy; t.idz = 1.0f / dz;
+  t.oodx = o.x * t.idx; t.oody = o.y * t.idy; t.oodz = o.z * t.idz;
+  t.o = o; t.d = d;
+  t.node = 0;  // the root is always an inner node
+  t.sp = 0;
   stack[0] = kSentinel;
-  int node = 0;  // root is always an inner node
-  float tbest = INFINITY;
-  unsigned rbest = 0xffffffffu;
-  int sbest = -1;
-  while (node != kSentinel) {
-    while (node >= 0 && node != kSentinel) {
-      const float4 *Np = S.nodes + 4 * (size_t)node;
-      float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
-      float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
-      float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
-      float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
-      float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
-      float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
-      float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
-      float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.f));
-      float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), tbest));
-      float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.f));
-      float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), tbest));
-      bool h0 = c0min <= c0max, h1 = c1min <= c1max;
-      int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
-      if (!h0 && !h1) {
-        node = stack[sp];
-        sp = sp > 0 ? sp - 1 : 0;
-      } else {
-        node = h0 ? ch0 : ch1;
-        if (h0 && h1) {
-          if (c1min < c0min) { int tmp = node; node = ch1; ch1 = tmp; }
-          stack[++sp] = ch1;
-        }
-      }
-    }
-    while (node < 0) {
-      int enc = ~node;
-      int first = enc >> 3, cnt = (enc & 7) + 1;
-      for (int k = 0; k < cnt; ++k) {
-        float t;
-        float4 T0, T1;
-        if (!tri_exact(S, first + k, o, d, tbest, t, T0, T1)) continue;
-        unsigned rank = (unsigned)f2i(T0.w);
-        // t <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
-        // and t == +inf never beats the initial INFINITY.
-        if (!ANY && !(t < tbest || (sbest >= 0 && rank < rbest))) continue;
-        if (!ref_box_pass(S, bo, d, f2i(T1.w))) continue;      // face not visible to the reference
-        tbest = t; rbest = rank; sbest = first + k;
-        if (ANY) { best_t = t; best_slot = sbest; return true; }
-      }
+  t.tbest = INFINITY;
+  t.rbest = 0xffffffffu;
+  t.sbest = -1;
+}
+
+// One macro step: descend through inner nodes to the next leaf, then test that leaf (and any
+// leaves popped right after it).  Returns true when the ray is finished.
+// CAREFUL = true : every candidate face is filtered by the reference's own box test before it
+//                  may win (exact, slow).
+// CAREFUL = false: closest-hit only - candidates are accepted unfiltered; the caller checks the
+//                  final winner's box once and re-runs in careful mode if that test fails.  The
+//                  unfiltered minimum, when its box passes, is also the filtered minimum.
+template <bool ANY, bool CAREFUL>
+RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
+  int node = t.node, sp = t.sp;
+  while (node >= 0 && node != kSentinel) {
+    const float4 *Np = S.nodes + 4 * (size_t)node;
+    float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
+    float c0lox = fmaf(n0.x, t.idx, -t.oodx), c0hix = fmaf(n0.y, t.idx, -t.oodx);
+    float c0loy = fmaf(n0.z, t.idy, -t.oody), c0hiy = fmaf(n0.w, t.idy, -t.oody);
+    float c0loz = fmaf(n2.x, t.idz, -t.oodz), c0hiz = fmaf(n2.y, t.idz, -t.oodz);
+    float c1lox = fmaf(n1.x, t.idx, -t.oodx), c1hix = fmaf(n1.y, t.idx, -t.oodx);
+    float c1loy = fmaf(n1.z, t.idy, -t.oody), c1hiy = fmaf(n1.w, t.idy, -t.oody);
+    float c1loz = fmaf(n2.z, t.idz, -t.oodz), c1hiz = fmaf(n2.w, t.idz, -t.oodz);
+    float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.f));
+    float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), t.tbest));
+    float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.f));
+    float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), t.tbest));
+    bool h0 = c0min <= c0max, h1 = c1min <= c1max;
+    int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
+    if (!h0 && !h1) {
       node = stack[sp];
       sp = sp > 0 ? sp - 1 : 0;
+    } else {
+      node = h0 ? ch0 : ch1;
+      if (h0 && h1) {
+        if (!ANY && c1min < c0min) { int tmp = node; node = ch1; ch1 = tmp; }
+        stack[++sp] = ch1;
+      }
     }
   }
-  best_t = tbest;
-  best_slot = sbest;
-  return sbest >= 0;
+  while (node < 0) {
+    int enc = ~node;
+    int first = enc >> 3, cnt = (enc & 7) + 1;
+    for (int k = 0; k < cnt; ++k) {
+      float tt;
+      float4 T0, T1;
+      if (!tri_exact(S, first + k, t.o, t.d, t.tbest, tt, T0, T1)) continue;
+      unsigned rank = (unsigned)f2i(T0.w);
+      // tt <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
+      // and t == +inf never beats the initial INFINITY.
+      if (!ANY && !(tt < t.tbest || (t.sbest >= 0 && rank < t.rbest))) continue;
+      if ((ANY || CAREFUL) && !ref_box_pass(S, bo, t.d, f2i(T1.w))) continue;  // invisible to the reference
+      t.tbest = ANY ? t.tbest : tt;
+      t.rbest = rank;
+      t.sbest = first + k;
+      if (ANY) { t.node = kSentinel; t.sp = 0; return true; }
+    }
+    node = stack[sp];
+    sp = sp > 0 ? sp - 1 : 0;
+  }
+  t.node = node;
+  t.sp = sp;
+  return node == kSentinel;
+}
+
+template <bool ANY>
+RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int &best_slot) {
+  int stack[kStackSize];
+  Trav t;
+  trav_init(t, o, d, stack);
+  while (!trav_step<ANY, ANY>(S, t, stack, bo)) {}
+  if (!ANY && t.sbest >= 0) {
+    // deferred visibility check of the winner (see trav_step); exact re-run on failure
+    const int box = f2i(RTP_LDG4(S.tris + 4 * (size_t)t.sbest + 1).w);
+    if (!ref_box_pass(S, bo, d, box)) {
+      trav_init(t, o, d, stack);
+      while (!trav_step<false, true>(S, t, stack, bo)) {}
+    }
+  }
+  best_t = t.tbest;
+  best_slot = t.sbest;
+  return t.sbest >= 0;
 }
 
 // ---- calcSingleColor after the shadow gate (flyscene.cpp:546-565) -----------------------------
