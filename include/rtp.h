@@ -85,7 +85,7 @@ typedef struct rtp_render_opts {
   int32_t flags;         /* RTP_RENDER_* */
 } rtp_render_opts;
 #define RTP_RENDER_DEFAULT 0
-#define RTP_RENDER_PROFILE 1 /* bracket each trace kernel with CUDA events -> ms_closest / ms_anyhit */
+#define RTP_RENDER_PROFILE 1 /* bracket each kernel with CUDA events -> ms_closest / ms_anyhit / ms_shade */
 
 typedef struct rtp_stats {
   int64_t rays_primary, rays_shadow, rays_reflection, hits;
@@ -93,8 +93,10 @@ typedef struct rtp_stats {
   float ms_total;       /* device time incl. output conversion, excl. H2D/D2H              */
   int32_t kernel_launches;
   int32_t n_bvh_nodes, n_triangles;
-  float ms_closest, ms_anyhit; /* with RTP_RENDER_PROFILE: summed device time of the closest-hit
-                                  kernels and of the shadow(any-hit)+shade kernels             */
+  /* with RTP_RENDER_PROFILE: summed device time per kernel kind */
+  float ms_closest; /* closest-hit traversal (calculateMinimumFace)                            */
+  float ms_anyhit;  /* shadow-ray traversal (shadow)                                           */
+  float ms_shade;   /* streaming kernels: ray generation, hit preparation, Phong, resolve      */
 } rtp_stats;
 
 /* ---- lifetime ---------------------------------------------------------------------------- */

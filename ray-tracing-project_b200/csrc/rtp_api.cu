@@ -59,7 +59,10 @@ struct Frame {
   int width = 0, height = 0, rank = 0, world = 1, max_depth = 0;
   int n_px = 0, tiles_x = 0;
   DevBuf<float4> fb, ksdeep, direct, ray_o0, ray_o1, ray_d0, ray_d1;
-  DevBuf<int> primface, hit_slot, tile_ids, local_of_tile;
+  int n_lights = 0, n_valid = 0;
+  DevBuf<float4> pbuf, nbuf;
+  DevBuf<int> primface, hit_slot, hitlist, tile_ids, local_of_tile;
+  DevBuf<unsigned char> occl;
   DevBuf<float> hit_t;
   DevBuf<float> out_rgb;
   DevBuf<unsigned char> out_rgb8;
@@ -74,7 +77,6 @@ struct rtp_scene {
   DevBuf<float4> nodes, tris, vnorm, boxes, materials, lights;
   DevBuf<int> face_of;
   DevBuf<int> counters;
-  DevBuf<unsigned long long> stats;
   DeviceScene dS;
   DeviceCamera cam;
   bool have_camera = false, have_lights = false;
@@ -82,7 +84,9 @@ struct rtp_scene {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
+  std::vector<int> kev_kind;     // 0 closest, 1 anyhit, 2 streaming (raygen/prep/accum/resolve)
   int kev_used = 0;
+  int last_primary = 0, last_depth = 0, last_lights = 0;
   cudaStream_t last_stream = nullptr;  // stream of the most recently enqueued frame
   bool has_last = false;
   int last_launches = 0;
@@ -158,7 +162,6 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
   if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
   if ((e = s->counters.ensure(kCtrInts)) != cudaSuccess) return cleanup(e, "alloc counters");
-  if ((e = s->stats.ensure(kStatCount)) != cudaSuccess) return cleanup(e, "alloc stats");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
   // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
   std::vector<float4>().swap(h.nodes);
@@ -250,19 +253,30 @@ int max_tile_count(int width, int height, int world) {
 // (Re)allocates the per-frame device state.  n_paths: pixels (tile-padded) or user rays.
 int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int world, int max_depth, int n_paths,
                  bool with_tiles) {
+  const int n_lights = std::max(s->dS.n_lights, 1);
   const bool same = f.width == width && f.height == height && f.rank == rank && f.world == world &&
-                    f.max_depth >= max_depth && f.n_px == n_paths;
+                    f.max_depth >= max_depth && f.n_px == n_paths && f.n_lights >= n_lights;
   if (same) return RTP_OK;
   f.width = width; f.height = height; f.rank = rank; f.world = world; f.max_depth = max_depth; f.n_px = n_paths;
+  f.n_lights = n_lights;
   f.tiles_x = (width + kTileDim - 1) / kTileDim;
   const size_t n = (size_t)std::max(n_paths, 1);
   CK(f.ksdeep.ensure(n));
   CK(f.direct.ensure(n * (size_t)max_depth));
   CK(f.ray_o0.ensure(n)); CK(f.ray_o1.ensure(n)); CK(f.ray_d0.ensure(n)); CK(f.ray_d1.ensure(n));
   CK(f.primface.ensure(n)); CK(f.hit_slot.ensure(n)); CK(f.hit_t.ensure(n));
+  CK(f.hitlist.ensure(n)); CK(f.pbuf.ensure(n)); CK(f.nbuf.ensure(n));
+  CK(f.occl.ensure(n * (size_t)n_lights));
+  f.n_valid = n_paths;
   if (with_tiles) {
     std::vector<int32_t> tiles, local;
     tile_tables(width, height, rank, world, tiles, local);
+    long long valid = 0;  // owned pixels inside the image = primary rays of this rank
+    for (int32_t t : tiles) {
+      const int x0 = (t % f.tiles_x) * kTileDim, y0 = (t / f.tiles_x) * kTileDim;
+      valid += (long long)std::min(kTileDim, width - x0) * std::min(kTileDim, height - y0);
+    }
+    f.n_valid = (int)valid;
     CK(f.tile_ids.upload(tiles, s->stream));
     CK(f.local_of_tile.upload(local, s->stream));
     CK(cudaStreamSynchronize(s->stream));
@@ -282,38 +296,47 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
   p.primface = f.primface.p; p.ksdeep = f.ksdeep.p; p.direct = f.direct.p;
   p.ray_o[0] = f.ray_o0.p; p.ray_o[1] = f.ray_o1.p; p.ray_d[0] = f.ray_d0.p; p.ray_d[1] = f.ray_d1.p;
   p.hit_t = f.hit_t.p; p.hit_slot = f.hit_slot.p;
-  p.counters = s->counters.p; p.stats = s->stats.p;
+  p.hitlist = f.hitlist.p; p.pbuf = f.pbuf.p; p.nbuf = f.nbuf.p; p.occl = f.occl.p;
+  p.counters = s->counters.p;
 }
 
-// Enqueues one frame: 2 * max_depth trace kernels + resolve.  Returns the number of launches.
-// profile: bracket every trace kernel with CUDA events (summed later by kernel_times).
-int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile = false) {
+// Enqueues one frame: raygen, then per level closest / prep / anyhit / accum, then resolve.
+// profile: bracket every kernel with CUDA events (summed per kernel kind by read_stats).
+int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile, int n_primary) {
   // one frame at a time per scene: counters and path buffers are shared between frames
   if (s->has_last && s->last_stream != st) CK(cudaStreamSynchronize(s->last_stream));
   CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), st));
-  CK(cudaMemsetAsync(s->stats.p, 0, kStatCount * sizeof(unsigned long long), st));
   int n = 0;
   s->kev_used = 0;
-  if (profile)
-    while ((int)s->kev.size() < 3 * p.max_depth + 1) {
+  s->kev_kind.clear();
+  auto mark = [&](int kind) -> cudaError_t {  // event before a kernel of `kind` (-1: end marker)
+    if (!profile) return cudaSuccess;
+    if (s->kev_used == (int)s->kev.size()) {
       cudaEvent_t e;
-      CK(cudaEventCreate(&e));
+      cudaError_t err = cudaEventCreate(&e);
+      if (err != cudaSuccess) return err;
       s->kev.push_back(e);
     }
+    s->kev_kind.push_back(kind);
+    return cudaEventRecord(s->kev[s->kev_used++], st);
+  };
+  CK(mark(2)); launch_raygen(p, st); ++n;
   for (int d = 0; d < p.max_depth; ++d) {
-    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
-    launch_closest(p, d, s->cfg, st);
-    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
-    launch_shade(p, d, s->cfg, st);
-    if (profile) CK(cudaEventRecord(s->kev[s->kev_used++], st));
-    n += 2;
+    CK(mark(0)); launch_closest(p, d, s->cfg, st);
+    CK(mark(2)); launch_prep(p, d, st);
+    CK(mark(1)); launch_anyhit(p, d, s->cfg, st);
+    CK(mark(2)); launch_accum(p, d, st);
+    n += 4;
   }
-  launch_resolve(p, st);
-  ++n;
+  CK(mark(2)); launch_resolve(p, st); ++n;
+  CK(mark(-1));
   CK(cudaGetLastError());
   s->last_stream = st;
   s->has_last = true;
   s->last_launches = n;
+  s->last_primary = n_primary;
+  s->last_depth = p.max_depth;
+  s->last_lights = p.S.n_lights;
   if (launches) *launches = n;
   return RTP_OK;
 }
@@ -330,20 +353,23 @@ int check_render_args(rtp_scene *s, const rtp_render_opts *o) {
 }
 
 int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
-  unsigned long long h[kStatCount];
-  CK(cudaMemcpyAsync(h, s->stats.p, sizeof h, cudaMemcpyDeviceToHost, stream));
+  int h[kCtrInts];
+  CK(cudaMemcpyAsync(h, s->counters.p, sizeof h, cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
-  for (int i = 0; i + 2 < s->kev_used; i += 3) {  // (before closest, between, after shade) per depth
-    float a = 0.f, b = 0.f;
-    CK(cudaEventElapsedTime(&a, s->kev[i], s->kev[i + 1]));
-    CK(cudaEventElapsedTime(&b, s->kev[i + 1], s->kev[i + 2]));
-    st->ms_closest += a;
-    st->ms_anyhit += b;
+  for (int i = 0; i + 1 < s->kev_used; ++i) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, s->kev[i], s->kev[i + 1]));
+    const int kind = s->kev_kind[(size_t)i];
+    (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : st->ms_shade) += ms;
   }
-  st->rays_primary = (int64_t)h[kStatPrimary];
-  st->rays_shadow = (int64_t)h[kStatShadow];
-  st->rays_reflection = (int64_t)h[kStatReflection];
-  st->hits = (int64_t)h[kStatHits];
+  // ray counting rule of SURVEY.md 8(d): 1 primary per pixel; per hit one shadow ray per light and,
+  // below the depth limit, one reflection ray
+  st->rays_primary = s->last_primary;
+  for (int d = 0; d < s->last_depth; ++d) {
+    st->hits += h[kCtrHits + d];
+    if (d > 0) st->rays_reflection += h[kCtrPaths + d];
+  }
+  st->rays_shadow = st->hits * s->last_lights;
   st->n_bvh_nodes = s->host.n_nodes;
   st->n_triangles = s->host.n_tris;
   return RTP_OK;
@@ -379,11 +405,12 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
   rc = ensure_frame(s, s->frame, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
   if (rc) return rc;
+  Frame &f = s->frame;
   FrameParams p;
-  fill_params(s, s->frame, *o, (float4 *)d_tiles, p);
+  fill_params(s, f, *o, (float4 *)d_tiles, p);
   int launches = 0;
   if (st) CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0);
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
   if (rc) return rc;
   if (st) {
     CK(cudaEventRecord(s->ev[1], cs));
@@ -430,7 +457,7 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   fill_params(s, f, *o, f.fb.p, p);
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0);
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
   if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
@@ -540,7 +567,7 @@ int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max
   p.n_user_rays = (int)n;
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches);
+  rc = enqueue_frame(s, p, cs, &launches, false, (int)n);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
   std::vector<float4> h((size_t)n);

@@ -1,20 +1,22 @@
 // rtp_kernels.cu - hand-written sm_100a kernels for the ray-tracing hot path.
 //
-// Wavefront pipeline, one bounce level = two persistent-warp kernels:
-//   k_closest(d): depth 0 generates the primary ray of every owned pixel on the fly
-//                 (traceRayThread, flyscene.cpp:299-314); deeper levels read the compacted
-//                 reflection-ray list.  BVH2 closest-hit traversal = calculateMinimumFace
-//                 (flyscene.cpp:373-396).
-//   k_shade(d)  : per hit: P, interpolated normal, then for every light one any-hit
-//                 traversal (= shadow, flyscene.cpp:510-526) and the Phong term
-//                 (calcSingleColor / calculateColor, flyscene.cpp:542-566,603-614); spawns the
-//                 reflection ray of the next level (flyscene.cpp:361-363) through a
-//                 warp-aggregated append.
-//   k_resolve   : folds the per-depth direct colours back with the reference's ks-of-deepest-hit
-//                 rule (flyscene.cpp:355-370) and writes r,g,b,face into the tile-major
-//                 framebuffer.
-// FP32 CUDA cores only; no tensor cores (not a dense contraction).
+// Wavefront pipeline.  Per bounce level d:
+//   k_trace<FrameClosest>  calculateMinimumFace for every ray of the level (flyscene.cpp:373-396)
+//   k_prep                 per hit: P = o + t*d, interpolated normal, compaction (flyscene.cpp:464,572-600)
+//   k_trace<FrameAny>      shadow() for every (hit, light) pair (flyscene.cpp:510-526)
+//   k_accum                calcSingleColor / calculateColor and the reflection-ray spawn
+//                          (flyscene.cpp:542-566,603-614,355-363)
+// plus k_raygen before level 0 (traceRayThread, flyscene.cpp:299-314) and k_resolve after the
+// last level (fold-back with the reference's ks-of-deepest-hit rule, flyscene.cpp:366-370).
+//
+// The two trace kernels are persistent: one CTA slot per SM resident set, every warp pulls rays
+// from a global cursor and REFILLS idle lanes (ballot + warp-aggregated atomic) whenever fewer
+// than kRefillBelow lanes still hold a ray, so divergent ray lengths do not leave lanes empty.
+// Per-thread short stack in local memory (L1-resident), 128-bit read-only loads of 64-byte nodes
+// and triangles.  FP32 CUDA cores only; no tensor cores (not a dense contraction).
 #include "rtp_kernels.h"
+
+#include <cstdlib>
 
 namespace rtp {
 
@@ -22,149 +24,265 @@ namespace {
 
 constexpr unsigned kFull = 0xffffffffu;
 
-__device__ __forceinline__ int warp_fetch(int *cursor, int lane) {
-  int base = 0;
-  if (lane == 0) base = atomicAdd(cursor, 32);
-  return __shfl_sync(kFull, base, 0);
-}
-
-__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(kFull, v, o);
-  return v;
-}
-
-// Primary ray of local path q: pixel (i, j) of an owned screen tile through the camera
-// (traceRayThread, flyscene.cpp:301-308), or the q-th caller-supplied ray (traceRay API).
-__device__ __forceinline__ bool primary_ray(const FrameParams &p, int q, v3 &o, v3 &d) {
-  if (p.user_rays) {
-    if (q >= p.n_user_rays) return false;
-    const float *r = p.user_rays + 6 * (size_t)q;
-    o = mk3(r[0], r[1], r[2]);
-    d = mk3(r[3], r[4], r[5]);
+// ---- jobs: where a trace kernel gets its rays from and where results go ----------------------
+struct FrameClosest {
+  static constexpr bool kAny = false;
+  DeviceScene S;
+  const float4 *ro, *rd;
+  float *hit_t;
+  int *hit_slot;
+  int *primface;  // depth 0 only
+  int *cursor;
+  const int *count_ptr;  // device counter (depth > 0) or null
+  int count_fixed;
+  __device__ __forceinline__ int count() const { return count_ptr ? *count_ptr : count_fixed; }
+  __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    const float4 d = rd[q];
+    if (d.w == 0.f) {  // no ray (pixel outside the image)
+      hit_t[q] = INFINITY;
+      hit_slot[q] = -2;
+      return false;
+    }
+    trav_init(t, xyz(ro[q]), xyz(d), stack);
     return true;
   }
-  int tile = __ldg(p.tile_ids + (q >> 10));
-  int x, y;
-  tile_pixel(q & (kTilePixels - 1), x, y);
-  const int i = (tile % p.tiles_x) * kTileDim + x;
-  const int j = (tile / p.tiles_x) * kTileDim + y;
-  o = mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
-  if (i >= p.width || j >= p.height) return false;
-  d = primary_dir(p.cam, i, j);
-  return true;
+  __device__ __forceinline__ v3 box_origin(int, const Trav &t) const { return t.o; }
+  __device__ __forceinline__ void finish(int q, Trav &t, int *stack) const;
+};
+
+struct FrameAny {
+  static constexpr bool kAny = true;
+  DeviceScene S;
+  const float4 *pbuf;
+  unsigned char *occl;
+  int *cursor;
+  const int *hits_ptr;
+  __device__ __forceinline__ int count() const { return *hits_ptr * S.n_lights; }
+  __device__ __forceinline__ v3 light_dir(int q, v3 P) const {
+    const int li = q % S.n_lights;
+    const float4 l0 = __ldg(S.lights + 2 * li);
+    v3 L = xyz(l0);
+    if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // flyscene.cpp:607
+    return L;
+  }
+  __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    const v3 P = xyz(pbuf[q / S.n_lights]);
+    const v3 L = light_dir(q, P);
+    trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);  // flyscene.cpp:512
+    return true;
+  }
+  __device__ __forceinline__ v3 box_origin(int q, const Trav &) const { return xyz(pbuf[q / S.n_lights]); }
+  __device__ __forceinline__ void finish(int q, Trav &t, int *) const { occl[q] = t.sbest >= 0 ? 1 : 0; }
+};
+
+struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
+  static constexpr bool kAny = false;
+  DeviceScene S;
+  const float *rays;
+  int *face;
+  float *tout;
+  int *cursor;
+  int n;
+  __device__ __forceinline__ int count() const { return n; }
+  __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    const float *r = rays + 6 * (size_t)q;
+    trav_init(t, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), stack);
+    return true;
+  }
+  __device__ __forceinline__ v3 box_origin(int, const Trav &t) const { return t.o; }
+  __device__ __forceinline__ void finish(int q, Trav &t, int *stack) const;
+};
+
+struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
+  static constexpr bool kAny = true;
+  DeviceScene S;
+  const float *rays;
+  unsigned char *occ;
+  int *cursor;
+  int n;
+  __device__ __forceinline__ int count() const { return n; }
+  __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    const float *r = rays + 6 * (size_t)q;
+    const v3 P = mk3(r[0], r[1], r[2]), L = mk3(r[3], r[4], r[5]);
+    trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
+    return true;
+  }
+  __device__ __forceinline__ v3 box_origin(int q, const Trav &) const {
+    const float *r = rays + 6 * (size_t)q;
+    return mk3(r[0], r[1], r[2]);
+  }
+  __device__ __forceinline__ void finish(int q, Trav &t, int *) const { occ[q] = t.sbest >= 0 ? 1 : 0; }
+};
+
+// Deferred visibility check of a closest-hit winner (rtp_device.h, trav_step): the unfiltered
+// minimum is exact unless the reference's own slab test rejects the winner's BoundingBox; then
+// (rare) the ray is re-traced with every candidate filtered.
+__device__ __noinline__ void closest_careful(const DeviceScene &S, Trav &t, int *stack) {
+  const v3 o = t.o, d = t.d;
+  trav_init(t, o, d, stack);
+  while (!trav_step<false, true>(S, t, stack, o)) {}
+}
+__device__ __forceinline__ void closest_verify(const DeviceScene &S, Trav &t, int *stack) {
+  if (t.sbest < 0) return;
+  const int box = f2i(__ldg(S.tris + 4 * (size_t)t.sbest + 1).w);
+  if (!ref_box_pass(S, t.o, t.d, box)) closest_careful(S, t, stack);
 }
 
-__global__ void __launch_bounds__(128) k_closest(const FrameParams p, const int depth) {
+__device__ __forceinline__ void FrameClosest::finish(int q, Trav &t, int *stack) const {
+  closest_verify(S, t, stack);
+  hit_t[q] = t.tbest;
+  hit_slot[q] = t.sbest;
+  if (primface) primface[q] = t.sbest >= 0 ? __ldg(S.face_of + t.sbest) : -1;
+}
+__device__ __forceinline__ void RaysClosest::finish(int q, Trav &t, int *stack) const {
+  closest_verify(S, t, stack);
+  face[q] = t.sbest >= 0 ? __ldg(S.face_of + t.sbest) : -1;
+  if (tout) tout[q] = t.tbest;
+}
+
+// ---- the persistent trace kernel -----------------------------------------------------------------
+template <class Job, int kRefillBelow>
+__global__ void __launch_bounds__(128, 8) k_trace(const Job job) {
   const int lane = threadIdx.x & 31;
-  const int count = depth == 0 ? p.n_px : p.counters[kCtrPaths + depth];
-  int *cursor = p.counters + kCtrFetch + 2 * depth;
-  const float4 *ro = p.ray_o[depth & 1], *rd = p.ray_d[depth & 1];
-  unsigned long long n_primary = 0;
+  const unsigned lt = (1u << lane) - 1u;
+  const int count = job.count();
+  int stack[kStackSize];
+  Trav t;
+  int q = 0;
+  bool have = false, exhausted = false;
   for (;;) {
-    const int base = warp_fetch(cursor, lane);
-    if (base >= count) break;
-    const int q = base + lane;
-    if (q >= count) continue;
-    v3 o, d;
-    bool valid = true;
-    if (depth == 0) {
-      valid = primary_ray(p, q, o, d);
-      p.ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-    } else {
-      o = xyz(ro[q]);
-      d = xyz(rd[q]);
+    unsigned act = __ballot_sync(kFull, have);
+    if (!exhausted && __popc(act) < kRefillBelow) {
+      // refill every idle lane with the next rays of the global list
+      const unsigned need = ~act;
+      const int n_need = __popc(need);
+      const int leader = __ffs(need) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(job.cursor, n_need);
+      base = __shfl_sync(kFull, base, leader);
+      exhausted = base + n_need >= count;
+      if (!have) {
+        q = base + __popc(need & lt);
+        if (q < count) have = job.init(q, t, stack);
+      }
+      act = __ballot_sync(kFull, have);
     }
-    float t = INFINITY;
-    int slot = -2;
-    if (valid) {
-      traverse<false>(p.S, o, d, o, t, slot);
-      ++n_primary;
+    if (act == 0) {
+      if (exhausted) break;
+      continue;
     }
-    p.hit_t[q] = t;
-    p.hit_slot[q] = slot;
-    if (depth == 0) p.primface[q] = slot >= 0 ? __ldg(p.S.face_of + slot) : (valid ? -1 : -2);
-  }
-  if (depth == 0) {
-    n_primary = warp_sum(n_primary);
-    if (lane == 0 && n_primary) atomicAdd(p.stats + kStatPrimary, n_primary);
+    if (have && trav_step<Job::kAny, false>(job.S, t, stack, job.box_origin(q, t))) {
+      job.finish(q, t, stack);
+      have = false;
+    }
   }
 }
 
-__global__ void __launch_bounds__(128) k_shade(const FrameParams p, const int depth) {
+// ---- streaming kernels ----------------------------------------------------------------------------
+// Depth-0 rays: pixel (i, j) of an owned screen tile through the camera (traceRayThread,
+// flyscene.cpp:301-308), or the q-th caller-supplied ray (traceRay API).
+__global__ void __launch_bounds__(256) k_raygen(const FrameParams p) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= p.n_px) return;
+  v3 o, d = mk3(0.f, 0.f, 0.f);
+  bool valid;
+  if (p.user_rays) {
+    valid = q < p.n_user_rays;
+    const float *r = p.user_rays + 6 * (size_t)(valid ? q : 0);
+    o = mk3(r[0], r[1], r[2]);
+    d = mk3(r[3], r[4], r[5]);
+  } else {
+    const int tile = __ldg(p.tile_ids + (q >> 10));
+    int x, y;
+    tile_pixel(q & (kTilePixels - 1), x, y);
+    const int i = (tile % p.tiles_x) * kTileDim + x;
+    const int j = (tile / p.tiles_x) * kTileDim + y;
+    o = mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+    valid = i < p.width && j < p.height;
+    if (valid) d = primary_dir(p.cam, i, j);
+  }
+  p.ray_o[0][q] = make_float4(o.x, o.y, o.z, i2f(q));
+  p.ray_d[0][q] = make_float4(d.x, d.y, d.z, valid ? 1.f : 0.f);
+  p.ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  p.primface[q] = valid ? -1 : -2;
+}
+
+// Per ray of the level that hit something: P, interpolated normal, and a slot in the compacted
+// hit list (warp-aggregated append keeps neighbouring pixels together).
+__global__ void __launch_bounds__(256) k_prep(const FrameParams p, const int depth) {
   const int lane = threadIdx.x & 31;
   const int count = depth == 0 ? p.n_px : p.counters[kCtrPaths + depth];
-  int *cursor = p.counters + kCtrFetch + 2 * depth + 1;
-  const float4 *ro = p.ray_o[depth & 1], *rd = p.ray_d[depth & 1];
-  float4 *no = p.ray_o[(depth + 1) & 1], *nd = p.ray_d[(depth + 1) & 1];
-  const bool spawn_level = depth + 1 < p.max_depth;
-  const int n_lights = p.S.n_lights;
-  unsigned long long n_hits = 0;
-  for (;;) {
-    const int base = warp_fetch(cursor, lane);
-    if (base >= count) break;
-    const int q = base + lane;
-    const int slot = q < count ? p.hit_slot[q] : -1;
-    const bool hit = slot >= 0;
-    v3 o2 = mk3(0.f, 0.f, 0.f), r = mk3(0.f, 0.f, 0.f);
-    int pixel = 0;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x * blockDim.x >= count) return;  // block-uniform
+  const int slot = q < count ? p.hit_slot[q] : -1;
+  const bool hit = slot >= 0;
+  v3 P = mk3(0.f, 0.f, 0.f), N = P;
+  if (hit) {
+    const v3 o = xyz(p.ray_o[depth & 1][q]), d = xyz(p.ray_d[depth & 1][q]);
+    P = vadd(o, vmuls(d, p.hit_t[q]));  // flyscene.cpp:464
+    N = interpolate_normal_slot(p.S, slot, P);
+  }
+  const unsigned m = __ballot_sync(kFull, hit);
+  if (m) {
+    const int leader = __ffs(m) - 1;
+    int h = 0;
+    if (lane == leader) h = atomicAdd(p.counters + kCtrHits + depth, __popc(m));
+    h = __shfl_sync(kFull, h, leader) + __popc(m & ((1u << lane) - 1u));
     if (hit) {
-      ++n_hits;
-      v3 o, d;
-      if (depth == 0) {
-        pixel = q;
-        primary_ray(p, q, o, d);
-      } else {
-        float4 a = ro[q];
-        o = xyz(a);
-        pixel = f2i(a.w);
-        d = xyz(rd[q]);
-      }
-      const float t = p.hit_t[q];
-      const v3 P = vadd(o, vmuls(d, t));  // flyscene.cpp:464
-      const float4 *T = p.S.tris + 4 * (size_t)slot;
-      const float4 *Nn = p.S.vnorm + 3 * (size_t)slot;
-      const float4 T2 = __ldg(T + 2);
-      const v3 normal = interpolate_normal(xyz(__ldg(T)), xyz(__ldg(T + 1)), xyz(T2), xyz(__ldg(T + 3)),
-                                           xyz(__ldg(Nn)), xyz(__ldg(Nn + 1)), xyz(__ldg(Nn + 2)), P);
-      const unsigned mat = (unsigned)f2i(T2.w) & kTriMatMask;
-      const float4 m0 = __ldg(p.S.materials + 3 * mat), m1 = __ldg(p.S.materials + 3 * mat + 1),
-                   m2 = __ldg(p.S.materials + 3 * mat + 2);
-      v3 sum = mk3(0.f, 0.f, 0.f);
-      for (int li = 0; li < n_lights; ++li) {  // calculateColor, flyscene.cpp:606-612
-        const float4 l0 = __ldg(p.S.lights + 2 * li), l1 = __ldg(p.S.lights + 2 * li + 1);
-        v3 L = xyz(l0);
-        if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // :607
-        const v3 inter = vadd(P, vmuls(L, (float)0.003));     // :512
-        float ts;
-        int ss;
-        if (traverse<true>(p.S, inter, L, P, ts, ss)) continue;  // shadowed: contributes nothing (:543-545)
-        sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, normal, L, xyz(l1), o, P));
-      }
-      p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
-      p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
-      if (spawn_level) {
-        r = reflect_dir(d, normal);                 // :361
-        o2 = vadd(P, vmuls(r, (float)0.001));       // :362
-      }
-    }
-    const bool spawn = hit && spawn_level;
-    const unsigned m = __ballot_sync(kFull, spawn);
-    if (m) {
-      const int leader = __ffs(m) - 1;
-      int dst = 0;
-      if (lane == leader) dst = atomicAdd(p.counters + kCtrPaths + depth + 1, __popc(m));
-      dst = __shfl_sync(kFull, dst, leader) + __popc(m & ((1u << lane) - 1u));
-      if (spawn) {
-        no[dst] = make_float4(o2.x, o2.y, o2.z, i2f(pixel));
-        nd[dst] = make_float4(r.x, r.y, r.z, 0.f);
-      }
+      p.hitlist[h] = q;
+      p.pbuf[h] = make_float4(P.x, P.y, P.z, i2f(slot));
+      p.nbuf[h] = make_float4(N.x, N.y, N.z, 0.f);
     }
   }
-  n_hits = warp_sum(n_hits);
-  if (lane == 0 && n_hits) {
-    atomicAdd(p.stats + kStatHits, n_hits);
-    atomicAdd(p.stats + kStatShadow, n_hits * (unsigned long long)n_lights);
-    if (spawn_level) atomicAdd(p.stats + kStatReflection, n_hits);
+}
+
+// Per hit: Phong over the unshadowed lights, clamp, remember ks, spawn the reflection ray.
+__global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int depth) {
+  const int lane = threadIdx.x & 31;
+  const int count = p.counters[kCtrHits + depth];
+  const int h = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x * blockDim.x >= count) return;  // block-uniform
+  const bool live = h < count;
+  const bool spawn = live && depth + 1 < p.max_depth;
+  v3 o2 = mk3(0.f, 0.f, 0.f), r = o2;
+  int pixel = 0;
+  if (live) {
+    const int q = p.hitlist[h];
+    const float4 ro = p.ray_o[depth & 1][q];
+    const v3 o = xyz(ro), d = xyz(p.ray_d[depth & 1][q]);
+    pixel = f2i(ro.w);
+    const float4 pb = p.pbuf[h];
+    const v3 P = xyz(pb), normal = xyz(p.nbuf[h]);
+    const int slot = f2i(pb.w);
+    const unsigned mat = (unsigned)f2i(__ldg(p.S.tris + 4 * (size_t)slot + 2).w) & kTriMatMask;
+    const float4 m0 = __ldg(p.S.materials + 3 * mat), m1 = __ldg(p.S.materials + 3 * mat + 1),
+                 m2 = __ldg(p.S.materials + 3 * mat + 2);
+    const int n_lights = p.S.n_lights;
+    v3 sum = mk3(0.f, 0.f, 0.f);
+    for (int li = 0; li < n_lights; ++li) {  // calculateColor, flyscene.cpp:606-612
+      if (p.occl[(size_t)h * n_lights + li]) continue;  // shadowed: contributes nothing (:543-545)
+      const float4 l0 = __ldg(p.S.lights + 2 * li), l1 = __ldg(p.S.lights + 2 * li + 1);
+      v3 L = xyz(l0);
+      if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // :607
+      sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, normal, L, xyz(l1), o, P));
+    }
+    p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
+    p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
+    if (spawn) {
+      r = reflect_dir(d, normal);            // :361
+      o2 = vadd(P, vmuls(r, (float)0.001));  // :362
+    }
+  }
+  const unsigned m = __ballot_sync(kFull, spawn);
+  if (m) {
+    const int leader = __ffs(m) - 1;
+    int dst = 0;
+    if (lane == leader) dst = atomicAdd(p.counters + kCtrPaths + depth + 1, __popc(m));
+    dst = __shfl_sync(kFull, dst, leader) + __popc(m & ((1u << lane) - 1u));
+    if (spawn) {
+      p.ray_o[(depth + 1) & 1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(pixel));
+      p.ray_d[(depth + 1) & 1][dst] = make_float4(r.x, r.y, r.z, 1.f);
+    }
   }
 }
 
@@ -218,39 +336,18 @@ __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_s
   if (hit) hit[idx] = f2i(v.w);
 }
 
-__global__ void __launch_bounds__(128) k_rays_closest(const DeviceScene S, const float *rays, long long n, int *face,
-                                                      float *t, int *cursor) {
-  const int lane = threadIdx.x & 31;
-  for (;;) {
-    const long long base = warp_fetch(cursor, lane);
-    if (base >= n) break;
-    const long long q = base + lane;
-    if (q >= n) continue;
-    const float *r = rays + 6 * q;
-    v3 o = mk3(r[0], r[1], r[2]), d = mk3(r[3], r[4], r[5]);
-    float tt;
-    int slot;
-    traverse<false>(S, o, d, o, tt, slot);
-    face[q] = slot >= 0 ? __ldg(S.face_of + slot) : -1;
-    if (t) t[q] = tt;
-  }
-}
+int g_refill = -1;  // RTP_REFILL: lanes-with-work threshold below which a warp refills (0 = batch mode)
 
-__global__ void __launch_bounds__(128) k_rays_anyhit(const DeviceScene S, const float *rays, long long n,
-                                                     unsigned char *occ, int *cursor) {
-  const int lane = threadIdx.x & 31;
-  for (;;) {
-    const long long base = warp_fetch(cursor, lane);
-    if (base >= n) break;
-    const long long q = base + lane;
-    if (q >= n) continue;
-    const float *r = rays + 6 * q;
-    v3 P = mk3(r[0], r[1], r[2]), L = mk3(r[3], r[4], r[5]);
-    const v3 inter = vadd(P, vmuls(L, (float)0.003));  // shadow(P, L), flyscene.cpp:512
-    float tt;
-    int slot;
-    occ[q] = traverse<true>(S, inter, L, P, tt, slot) ? 1 : 0;
+template <class Job>
+void launch_trace(const Job &job, int blocks, int threads, cudaStream_t st) {
+  if (g_refill < 0) {
+    const char *e = std::getenv("RTP_REFILL");
+    g_refill = e ? std::atoi(e) : 24;
   }
+  if (g_refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job);
+  else if (g_refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job);
+  else if (g_refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job);
+  else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job);
 }
 
 }  // namespace
@@ -259,21 +356,48 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   int b0 = 1, b1 = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_closest, cfg.threads, 0);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_shade, cfg.threads, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_trace<FrameClosest, 24>, cfg.threads, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny, 24>, cfg.threads, 0);
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
-  cfg.blocks_shade = sms * (b1 > 0 ? b1 : 1);
+  cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
 }
 
+void launch_raygen(const FrameParams &p, cudaStream_t st) { k_raygen<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
+
 void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
-  k_closest<<<cfg.blocks_closest, cfg.threads, 0, st>>>(p, depth);
+  FrameClosest j;
+  j.S = p.S;
+  j.ro = p.ray_o[depth & 1];
+  j.rd = p.ray_d[depth & 1];
+  j.hit_t = p.hit_t;
+  j.hit_slot = p.hit_slot;
+  j.primface = depth == 0 ? p.primface : nullptr;
+  j.cursor = p.counters + kCtrFetchClosest + depth;
+  j.count_ptr = depth == 0 ? nullptr : p.counters + kCtrPaths + depth;
+  j.count_fixed = p.n_px;
+  launch_trace(j, cfg.blocks_closest, cfg.threads, st);
 }
-void launch_shade(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
-  k_shade<<<cfg.blocks_shade, cfg.threads, 0, st>>>(p, depth);
+
+void launch_prep(const FrameParams &p, int depth, cudaStream_t st) {
+  k_prep<<<(p.n_px + 255) / 256, 256, 0, st>>>(p, depth);
 }
-void launch_resolve(const FrameParams &p, cudaStream_t st) {
-  k_resolve<<<(p.n_px + 255) / 256, 256, 0, st>>>(p);
+
+void launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+  FrameAny j;
+  j.S = p.S;
+  j.pbuf = p.pbuf;
+  j.occl = p.occl;
+  j.cursor = p.counters + kCtrFetchAny + depth;
+  j.hits_ptr = p.counters + kCtrHits + depth;
+  launch_trace(j, cfg.blocks_any, cfg.threads, st);
 }
+
+void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
+  k_accum<<<(p.n_px + 255) / 256, 256, 0, st>>>(p, depth);
+}
+
+void launch_resolve(const FrameParams &p, cudaStream_t st) { k_resolve<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
+
 void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile, int width, int height,
                    int world, int only_rank, float *rgb, unsigned char *rgb8, int *hit, cudaStream_t st) {
   const long long n = (long long)width * height;
@@ -281,13 +405,19 @@ void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of
   k_untile<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(all, rank_stride_f4, local_of_tile, width, height, tiles_x,
                                                         world, only_rank, rgb, rgb8, hit);
 }
+
 void launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
                          const LaunchCfg &cfg, cudaStream_t st) {
-  k_rays_closest<<<cfg.blocks_closest, cfg.threads, 0, st>>>(S, rays, n, face, t, cursor);
+  RaysClosest j;
+  j.S = S; j.rays = rays; j.face = face; j.tout = t; j.cursor = cursor; j.n = (int)n;
+  launch_trace(j, cfg.blocks_closest, cfg.threads, st);
 }
+
 void launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st) {
-  k_rays_anyhit<<<cfg.blocks_closest, cfg.threads, 0, st>>>(S, rays, n, occ, cursor);
+  RaysAny j;
+  j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
+  launch_trace(j, cfg.blocks_any, cfg.threads, st);
 }
 
 }  // namespace rtp

@@ -6,43 +6,55 @@
 
 namespace rtp {
 
-// counters[] layout (ints)
-constexpr int kCtrPaths = 0;    // [depth]   number of live paths entering depth
-constexpr int kCtrFetch = 16;   // [2*depth + {0: closest, 1: shade}] persistent-warp batch cursors
-constexpr int kCtrAux = 48;     // ray-batch API cursor
+// counters[] layout (ints), zeroed at the start of every frame
+constexpr int kCtrPaths = 0;          // [depth] rays entering depth (depth 0: n_px, kept on the host)
+constexpr int kCtrHits = 16;          // [depth] hits found at depth
+constexpr int kCtrFetchClosest = 32;  // [depth] persistent-warp ray cursor of k_closest
+constexpr int kCtrFetchAny = 48;      // [depth] persistent-warp ray cursor of k_anyhit
+constexpr int kCtrAux = 62;           // ray-batch API cursor
 constexpr int kCtrInts = 64;
-// stats[] layout (unsigned long long)
-constexpr int kStatPrimary = 0, kStatShadow = 1, kStatReflection = 2, kStatHits = 3, kStatCount = 4;
 
 struct FrameParams {
   DeviceScene S;
   DeviceCamera cam;
   int width, height, tiles_x;
-  int n_px;             // local pixels = owned tiles * 1024 (tile-major order)
-  const int *tile_ids;  // owned tile -> global tile id
+  int n_px;                // local paths at depth 0 = owned tiles * 1024 (tile-major) or user rays
+  const int *tile_ids;     // owned tile -> global tile id
   const float *user_rays;  // non-null: depth-0 rays come from here (n x 6) instead of the camera
   int n_user_rays;
   int max_depth;
   float bg[3];
-  float4 *fb;           // out, tile-major: r, g, b, bit-cast primary face id
-  int *primface;        // [n_px]
-  float4 *ksdeep;       // [n_px] ks of the deepest hit, .w = hit-chain length bits
-  float4 *direct;       // [max_depth][n_px] clamped direct colour per depth
-  float4 *ray_o[2];     // ping-pong path buffers: (origin, bit-cast local pixel)
-  float4 *ray_d[2];     //                         (direction, -)
-  float *hit_t;         // [n_px] closest-hit t of the current depth
-  int *hit_slot;        // [n_px] closest-hit triangle slot (-1 miss, -2 pixel outside the image)
+  float4 *fb;        // out, tile-major: r, g, b, bit-cast primary face id
+  int *primface;     // [n_px] primary face id (-1 background, -2 pixel outside the image)
+  float4 *ksdeep;    // [n_px] ks of the deepest hit, .w = hit-chain length bits
+  float4 *direct;    // [max_depth][n_px] clamped direct colour per depth
+  float4 *ray_o[2];  // ping-pong ray lists: (origin, bit-cast local pixel)
+  float4 *ray_d[2];  //                      (direction, 1 = live / 0 = no ray)
+  float *hit_t;      // [n_px] closest-hit t of the current depth
+  int *hit_slot;     // [n_px] closest-hit triangle slot (-1 miss, -2 no ray)
+  int *hitlist;      // [n_px] compacted list of paths that hit something at the current depth
+  float4 *pbuf;      // [n_px] per hit: (P, bit-cast triangle slot)
+  float4 *nbuf;      // [n_px] per hit: (interpolated normal, -)
+  unsigned char *occl;  // [n_px * n_lights] per hit and light: 1 = shadowed
   int *counters;
-  unsigned long long *stats;
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_shade = 0, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, threads = 128;
 };
 void query_launch_cfg(int device, LaunchCfg &cfg);
 
+// depth-0 rays of every owned pixel (traceRayThread, flyscene.cpp:299-314) or the caller's rays
+void launch_raygen(const FrameParams &p, cudaStream_t st);
+// calculateMinimumFace for every ray of `depth` (flyscene.cpp:373-396)
 void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
-void launch_shade(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// per hit: P, interpolated normal, compaction (flyscene.cpp:464,572-600)
+void launch_prep(const FrameParams &p, int depth, cudaStream_t st);
+// shadow() for every (hit, light) pair (flyscene.cpp:510-526)
+void launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// calcSingleColor / calculateColor + reflection-ray spawn (flyscene.cpp:542-566,603-614,355-363)
+void launch_accum(const FrameParams &p, int depth, cudaStream_t st);
+// fold-back of the per-depth colours (flyscene.cpp:366-370) -> tile-major framebuffer
 void launch_resolve(const FrameParams &p, cudaStream_t st);
 // tile-major buffers of all ranks -> row-major planes (any of the outputs may be null).
 // only_rank >= 0: `all` holds just that rank's tiles; pixels of other ranks are left untouched.

@@ -107,6 +107,22 @@ def test_tile_sharding_is_bitwise_equal_to_one_gpu(rtp):
     s.close()
 
 
+def test_reference_box_filter_is_reproduced(rtp, po):
+    """Faces whose BoundingBox fails the reference's own slab test are invisible (Q11/Q13): with
+    artificially shrunken boxes this hits the deferred visibility check and the exact re-run."""
+    from test_hostsim import shrunken_boxes_mesh
+    m2 = shrunken_boxes_mesh(po)
+    c = load_case("dodge_c2")
+    w, h = 320, 180
+    s = make_scene(rtp, m2, with_boxes=True)
+    s.set_lights(c["point_lights"], None)
+    s.set_camera(w, h, c["view"])
+    out = s.render(w, h, max_depth=3)
+    s.close()
+    o = po.render(m2, w, h, view=c["view"], max_depth=3, point_lights=c["point_lights"], threads=8)
+    check_image(out["rgb"].reshape(-1, 3), out["hit"].ravel(), o["rgb"], o["hit"])
+
+
 def test_ray_batch_api_matches_oracle(rtp, po):
     m = load_golden_mesh("dodgeColorTest")
     rng = np.random.default_rng(11)

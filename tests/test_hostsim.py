@@ -47,6 +47,30 @@ def test_caller_supplied_boxes_restrict_visibility(hostsim, rtp, po):
     assert set(np.unique(a["hit"])) <= set(keep.tolist()) | {-1}
 
 
+def shrunken_boxes_mesh(po, model="dodgeColorTest", factor=0.8):
+    """BoundingBoxes shrunk towards their centres: the reference's slab test (flyscene.cpp:484-507)
+    now rejects boxes whose faces a ray does hit, so those faces become invisible (Q11/Q13) -
+    exercises the per-candidate visibility filter and the deferred check + exact re-run."""
+    m = load_golden_mesh(model)
+    c = 0.5 * (m.boxes[:, :3] + m.boxes[:, 3:])
+    b = np.concatenate([c + factor * (m.boxes[:, :3] - c), c + factor * (m.boxes[:, 3:] - c)], 1).astype(np.float32)
+    m2 = po.Mesh(m.verts, m.normals, m.faces, m.face_mat, m.materials, None, m.shape)
+    return m2.set_boxes(b, m.box_off, m.box_faces)
+
+
+def test_reference_box_filter_is_reproduced(hostsim, rtp, po):
+    m2 = shrunken_boxes_mesh(po)
+    c = load_case("dodge_c2")
+    s = HostSimScene(hostsim, rtp, m2, with_boxes=True)
+    a = s.render(96, 54, c["view"], 3, c["point_lights"], None)
+    s.close()
+    b = po.render(m2, 96, 54, view=c["view"], max_depth=3, point_lights=c["point_lights"])
+    full = po.render(load_golden_mesh("dodgeColorTest"), 96, 54, view=c["view"], max_depth=3, point_lights=c["point_lights"])
+    assert (b["hit"] != full["hit"]).sum() > 50, "the shrunken boxes must actually change the image"
+    assert np.array_equal(a["hit"], b["hit"]) and bits_equal(a["t"], b["t"]).all()
+    assert bits_equal(a["rgb"], b["rgb"]).all()
+
+
 def test_ray_batches_match_oracle(hostsim, rtp, po):
     m = load_golden_mesh("dodgeColorTest")
     rng = np.random.default_rng(7)
