@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libflyscene_b200.so")
+LIB_PATH = os.environ.get("RTP_LIB") or os.path.join(HERE, "libflyscene_b200.so")  # RTP_LIB: kernel-variant A/B runs
 
 _f32p = C.POINTER(C.c_float)
 _i32p = C.POINTER(C.c_int32)

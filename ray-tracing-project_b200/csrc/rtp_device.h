@@ -158,6 +158,7 @@ struct Trav {
   float tbest;
   unsigned rbest;
   int sbest;
+  bool careful;  // closest-hit re-run: filter every candidate by the reference's box test
 };
 
 RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
@@ -174,16 +175,19 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
   t.tbest = INFINITY;
   t.rbest = 0xffffffffu;
   t.sbest = -1;
+  t.careful = false;
 }
 
 // One macro step: descend through inner nodes to the next leaf, then test that leaf (and any
 // leaves popped right after it).  Returns true when the ray is finished.
-// CAREFUL = true : every candidate face is filtered by the reference's own box test before it
-//                  may win (exact, slow).
-// CAREFUL = false: closest-hit only - candidates are accepted unfiltered; the caller checks the
-//                  final winner's box once and re-runs in careful mode if that test fails.  The
-//                  unfiltered minimum, when its box passes, is also the filtered minimum.
-template <bool ANY, bool CAREFUL>
+// t.careful = true : every candidate face is filtered by the reference's own box test before it
+//                    may win (exact, slow).
+// t.careful = false: closest-hit only - candidates are accepted unfiltered; the caller checks the
+//                    final winner's box once (closest_needs_rerun) and re-runs in careful mode if
+//                    that test fails.  The unfiltered minimum, when its box passes, is also the
+//                    filtered minimum.  A runtime flag (not a second instantiation) keeps the whole
+//                    traversal state in registers: no out-of-line re-trace function.
+template <bool ANY>
 RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
   int node = t.node, sp = t.sp;
   while (node >= 0 && node != kSentinel) {
@@ -202,8 +206,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
     bool h0 = c0min <= c0max, h1 = c1min <= c1max;
     int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
     if (!h0 && !h1) {
-      node = stack[sp];
-      sp = sp > 0 ? sp - 1 : 0;
+      node = stack[sp--];  // stack[0] is the sentinel: popping it ends the ray, sp is not used after
     } else {
       node = h0 ? ch0 : ch1;
       if (h0 && h1) {
@@ -223,18 +226,30 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
       // tt <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
       // and t == +inf never beats the initial INFINITY.
       if (!ANY && !(tt < t.tbest || (t.sbest >= 0 && rank < t.rbest))) continue;
-      if ((ANY || CAREFUL) && !ref_box_pass(S, bo, t.d, f2i(T1.w))) continue;  // invisible to the reference
+      if ((ANY || t.careful) && !ref_box_pass(S, bo, t.d, f2i(T1.w))) continue;  // invisible to the reference
       t.tbest = ANY ? t.tbest : tt;
       t.rbest = rank;
       t.sbest = first + k;
       if (ANY) { t.node = kSentinel; t.sp = 0; return true; }
     }
-    node = stack[sp];
-    sp = sp > 0 ? sp - 1 : 0;
+    node = stack[sp--];
   }
   t.node = node;
   t.sp = sp;
   return node == kSentinel;
+}
+
+// Deferred visibility check of a finished closest-hit ray: when the reference's own slab test
+// rejects the winner's BoundingBox the ray is re-initialised in careful mode (rare) and the caller
+// keeps stepping it.
+RTP_HD bool closest_needs_rerun(const DeviceScene &S, Trav &t, int *stack) {
+  if (t.careful || t.sbest < 0) return false;
+  const int box = f2i(RTP_LDG4(S.tris + 4 * (size_t)t.sbest + 1).w);
+  if (ref_box_pass(S, t.o, t.d, box)) return false;
+  const v3 o = t.o, d = t.d;
+  trav_init(t, o, d, stack);
+  t.careful = true;
+  return true;
 }
 
 template <bool ANY>
@@ -242,15 +257,9 @@ RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int
   int stack[kStackSize];
   Trav t;
   trav_init(t, o, d, stack);
-  while (!trav_step<ANY, ANY>(S, t, stack, bo)) {}
-  if (!ANY && t.sbest >= 0) {
-    // deferred visibility check of the winner (see trav_step); exact re-run on failure
-    const int box = f2i(RTP_LDG4(S.tris + 4 * (size_t)t.sbest + 1).w);
-    if (!ref_box_pass(S, bo, d, box)) {
-      trav_init(t, o, d, stack);
-      while (!trav_step<false, true>(S, t, stack, bo)) {}
-    }
-  }
+  do {
+    while (!trav_step<ANY>(S, t, stack, bo)) {}
+  } while (!ANY && closest_needs_rerun(S, t, stack));
   best_t = t.tbest;
   best_slot = t.sbest;
   return t.sbest >= 0;
