@@ -1,0 +1,198 @@
+// raytrace_main.cpp - headless replacement of the reference's app shell (src/main.cpp): what its
+// key T does (main.cpp:68-69 -> Flyscene::raytraceScene -> result.ppm), driven by arguments instead
+// of a GLFW window.  Also the scene-dump tool of the CPU-only tests (--dump-scene needs no GPU).
+//
+//   raytrace [--model DIR/FILE.obj] [--size W H] [--depth MAX_DEPTH] [--fovy DEG]
+//            [--view m0..m11] [--light x y z r g b]... [--dirlight x y z r g b]... [--nolights]
+//            [--soft x y z r g b RADIUS N] [--out result.ppm] [--device N] [--dump-scene PREFIX]
+//            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
+//            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
+#include <array>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "flyscene.hpp"
+
+namespace {
+
+template <class T>
+void dump(const std::string &path, const std::vector<T> &v) {
+  FILE *f = fopen(path.c_str(), "wb");
+  if (!f) { perror(path.c_str()); exit(3); }
+  if (!v.empty()) fwrite(v.data(), sizeof(T), v.size(), f);
+  fclose(f);
+}
+
+int usage() {
+  fprintf(stderr, "usage: raytrace [--model path.obj] [--size W H] [--depth D] [--fovy deg] [--view 12 floats]\n"
+                  "                [--light x y z r g b] [--dirlight x y z r g b] [--nolights] [--soft x y z r g b radius n]\n"
+                  "                [--out file.ppm] [--device n] [--dump-scene prefix]\n");
+  return 2;
+}
+
+// Loads and flattens exactly as Flyscene::initialize does, without touching CUDA.
+int dump_scene(const std::string &model, const std::string &prefix, int min_faces) {
+  Tucano::Mesh mesh;
+  std::vector<Tucano::Material::Mtl> materials;
+  Tucano::MeshImporter::loadObjFile(mesh, materials, model);
+  mesh.normalizeModelMatrix();
+  const int V = mesh.getNumberOfVertices(), F = mesh.getNumberOfFaces();
+  if (F == 0) return 1;
+  std::vector<float> verts, normals, fnormal, mats, shape;
+  std::vector<int> faces, fmat;
+  for (int i = 0; i < V; ++i) {
+    for (int c = 0; c < 4; ++c) verts.push_back(mesh.getVertex(i)[c]);
+    for (int c = 0; c < 3; ++c) normals.push_back(mesh.getNormal(i)[c]);
+  }
+  for (int i = 0; i < F; ++i) {
+    const Tucano::Face &f = mesh.getFace(i);
+    for (int c = 0; c < 3; ++c) { faces.push_back((int)f.vertex_ids[(size_t)c]); fnormal.push_back(f.normal[c]); }
+    fmat.push_back(f.material_id);
+  }
+  for (const Tucano::Material::Mtl &m : materials) {
+    for (int c = 0; c < 3; ++c) mats.push_back(m.getAmbient()[c]);
+    for (int c = 0; c < 3; ++c) mats.push_back(m.getDiffuse()[c]);
+    for (int c = 0; c < 3; ++c) mats.push_back(m.getSpecular()[c]);
+    mats.push_back(m.getShininess()); mats.push_back(m.getOpticalDensity()); mats.push_back(m.getDissolveFactor());
+  }
+  const Eigen::Affine3f sm = mesh.getShapeModelMatrix();
+  shape.assign(sm.data(), sm.data() + 12);
+  // the BoundingBox list through the mirror class, as Flyscene::generateBoundingBoxes drives it
+  BoundingBox::mesh = &mesh;
+  BoundingBox *root = new BoundingBox(true);
+  root->fitMesh();
+  bool notDone = true;
+  while (notDone) {
+    notDone = false;
+    std::vector<BoundingBox *> current = BoundingBox::boxes;
+    for (BoundingBox *b : current)
+      if (b->getNumberOfFaces() > min_faces && (!b->failed[0] || !b->failed[1] || !b->failed[2])) {
+        BoundingBox *nb = b->splitBox();
+        while (b == nb) nb = b->splitBox();
+        notDone = true;
+      }
+  }
+  std::vector<float> bounds;
+  std::vector<int> box_off, box_faces;
+  BoundingBox::exportBoxes(bounds, box_off, box_faces);
+  BoundingBox::deconstruct();
+  dump(prefix + ".verts.f32", verts); dump(prefix + ".normals.f32", normals); dump(prefix + ".fnormal.f32", fnormal);
+  dump(prefix + ".materials.f32", mats); dump(prefix + ".shape.f32", shape); dump(prefix + ".faces.i32", faces);
+  dump(prefix + ".fmat.i32", fmat); dump(prefix + ".boxes.f32", bounds); dump(prefix + ".box_off.i32", box_off);
+  dump(prefix + ".box_faces.i32", box_faces);
+  return 0;
+}
+
+// Primary rays exactly as traceRayThread forms them (flyscene.cpp:301-308), host side only.
+int dump_rays(const std::string &prefix, int W, int H, float fovy, const float *view) {
+  Tucano::Flycamera cam;
+  cam.setPerspectiveMatrix(fovy, W / (float)H, 0.1f, 100.0f);
+  cam.setViewport(Eigen::Vector2f((float)W, (float)H));
+  if (view) {
+    Eigen::Affine3f v;
+    std::memcpy(v.m, view, 12 * sizeof(float));
+    cam.setViewMatrix(v);
+  }
+  const Eigen::Vector3f origin = cam.getCenter();
+  std::vector<float> o = {origin[0], origin[1], origin[2]}, d;
+  for (int j = 0; j < H; ++j)
+    for (int i = 0; i < W; ++i) {
+      const Eigen::Vector3f dir = (cam.screenToWorld(Eigen::Vector2f((float)i, (float)j)) - origin).normalized();
+      for (int c = 0; c < 3; ++c) d.push_back(dir[c]);
+    }
+  const Eigen::Affine3f vm = cam.getViewMatrix();
+  std::vector<float> vmat(vm.data(), vm.data() + 12);
+  dump(prefix + ".origin.f32", o); dump(prefix + ".dir.f32", d); dump(prefix + ".view.f32", vmat);
+  return 0;
+}
+
+int ppm_from_f32(const std::string &in, const std::string &out, int W, int H) {
+  FILE *f = fopen(in.c_str(), "rb");
+  if (!f) { perror(in.c_str()); return 3; }
+  std::vector<float> px(3 * (size_t)W * H);
+  const size_t got = fread(px.data(), sizeof(float), px.size(), f);
+  fclose(f);
+  if (got != px.size()) { fprintf(stderr, "raytrace: %s holds %zu floats, expected %zu\n", in.c_str(), got, px.size()); return 3; }
+  std::vector<std::vector<Eigen::Vector3f>> data((size_t)H, std::vector<Eigen::Vector3f>((size_t)W));
+  for (int j = 0; j < H; ++j)
+    for (int i = 0; i < W; ++i) {
+      const float *p = &px[3 * ((size_t)j * W + i)];
+      data[(size_t)j][(size_t)i] = Eigen::Vector3f(p[0], p[1], p[2]);
+    }
+  Tucano::ImageImporter::writePPMImage(out, data);
+  return 0;
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+  std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out;
+  int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
+  float fovy = 60.f;
+  bool has_view = false, nolights = false;
+  float view[12];
+  std::vector<std::array<float, 6>> lights, dirlights;
+  std::vector<std::array<float, 8>> soft;
+  auto need = [&](int i, int n) { if (i + n >= argc) exit(usage()); };
+  for (int i = 1; i < argc; ++i) {
+    std::string a = argv[i];
+    if (a == "--model") { need(i, 1); model = argv[++i]; }
+    else if (a == "--size") { need(i, 2); W = atoi(argv[++i]); H = atoi(argv[++i]); }
+    else if (a == "--depth") { need(i, 1); depth = atoi(argv[++i]); }
+    else if (a == "--fovy") { need(i, 1); fovy = (float)atof(argv[++i]); }
+    else if (a == "--device") { need(i, 1); device = atoi(argv[++i]); }
+    else if (a == "--out") { need(i, 1); out = argv[++i]; }
+    else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
+    else if (a == "--dump-rays") { need(i, 1); rays_prefix = argv[++i]; }
+    else if (a == "--ppm-from-f32") { need(i, 2); f32_in = argv[++i]; f32_out = argv[++i]; }
+    else if (a == "--nolights") nolights = true;
+    else if (a == "--view") { need(i, 12); has_view = true; for (int k = 0; k < 12; ++k) view[k] = strtof(argv[++i], nullptr); }
+    else if (a == "--light" || a == "--dirlight") {
+      need(i, 6);
+      std::array<float, 6> l;
+      for (int k = 0; k < 6; ++k) l[(size_t)k] = strtof(argv[++i], nullptr);
+      (a == "--light" ? lights : dirlights).push_back(l);
+    } else if (a == "--soft") {
+      need(i, 8);
+      std::array<float, 8> l;
+      for (int k = 0; k < 8; ++k) l[(size_t)k] = strtof(argv[++i], nullptr);
+      soft.push_back(l);
+    } else return usage();
+  }
+  if (!dump_prefix.empty()) return dump_scene(model, dump_prefix, 300);
+  if (!rays_prefix.empty()) return dump_rays(rays_prefix, W, H, fovy, has_view ? view : nullptr);
+  if (!f32_in.empty()) return ppm_from_f32(f32_in, f32_out, W, H);
+
+  Flyscene *flyscene = new Flyscene();  // main.cpp:40-41
+  const size_t slash = model.find_last_of('/');
+  flyscene->MODEL_DIR = slash == std::string::npos ? "" : model.substr(0, slash + 1);
+  flyscene->OBJECT_NAME = slash == std::string::npos ? model : model.substr(slash + 1);
+  flyscene->OUTPUT_NAME = out;
+  flyscene->DEVICE = device;
+  flyscene->max_depth = depth;
+  flyscene->initialize(W, H);
+  if (!flyscene->ok()) { fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str()); return 1; }
+  flyscene->getCamera()->setPerspectiveMatrix(fovy, W / (float)H, 0.1f, 100.0f);
+  if (has_view) {
+    Eigen::Affine3f v;
+    std::memcpy(v.m, view, sizeof view);
+    flyscene->getCamera()->setViewMatrix(v);
+  }
+  if (nolights || !lights.empty() || !dirlights.empty() || !soft.empty()) flyscene->lights.clear();  // key C, main.cpp:72
+  for (auto &l : lights) flyscene->lights.push_back({Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5])});
+  for (auto &l : dirlights)
+    flyscene->dirLights.push_back(std::make_tuple(Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5]), Eigen::Quaternion<float>()));
+  for (auto &l : soft) {  // what addLight's "s" branch does (flyscene.cpp:213-236)
+    std::pair<Eigen::Vector3f, Eigen::Vector3f> light(Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5]));
+    flyscene->sphericalLight(light, l[6], (int)l[7]);
+    light.second /= (float)((int)l[7] + 1);
+    flyscene->lights.push_back(light);
+  }
+  flyscene->raytraceScene();  // key T
+  const bool ok = flyscene->lastError().empty();
+  if (!ok) fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str());
+  delete flyscene;
+  return ok ? 0 : 1;
+}

@@ -43,15 +43,19 @@ CASES = [
     ("glas_nan", "glas.obj", 64, 64, None, 2, None, None),                        # Ns 506.25 -> NaN pixels (Q8)
     ("dodge_c1", "dodgeColorTest.obj", 64, 64, None, 2, None, None),              # the reference's default scene
     ("dodge_c2", "dodgeColorTest.obj", 96, 54, rotview(2.1, -0.3, [0.05, 0.1, -1.5]), 4, L4, None),  # C2 reduced
+    # tests/golden/quirks.obj + quirks.mtl are authored for this repo (not reference files): CRLF, #vn != #v,
+    # unknown usemtl, a quad + a 2-ref f line re-cut into triples, v/t/n forms, a tab-indented MTL key
+    ("quirks", os.path.join(HERE, "quirks.obj"), 48, 48, None, 3, None, None),
 ]
 
 
 def main():
     meshes = {}
     for name, model, w, h, view, md, pl, dl in CASES:
-        r = po.ref_run(po.ref_model(model), w, h, view=view, max_depth=md, point_lights=pl, dir_lights=dl,
+        r = po.ref_run(model if os.path.isabs(model) else po.ref_model(model), w, h, view=view, max_depth=md, point_lights=pl, dir_lights=dl,
                        dump_scene=True)
         m = r["mesh"]
+        model = os.path.basename(model)
         if model not in meshes:
             meshes[model] = m
             np.savez_compressed(os.path.join(HERE, "mesh_" + model.replace(".obj", "") + ".npz"),
