@@ -217,22 +217,16 @@ def run_ours(args, wl, rtp):
     scene.set_lights(wl["lights"], None)
     scene.set_camera(w, h, wl["view"])
     info = scene.info()
-    stride = rtp.tile_buffer_bytes(w, h, rank, world)
-    tiles = torch.zeros(stride // 4, dtype=torch.float32, device=dev)
-    gathered = torch.zeros(world * stride // 4, dtype=torch.float32, device=dev) if (world > 1 and rank == 0) else None
+    mg = importlib.import_module("ray-tracing-project_b200.multigpu")
+    tg = mg.TileGather(w, h, rank, world, dev, rtp)
     rgb8 = torch.zeros(w * h * 3, dtype=torch.uint8, device=dev) if rank == 0 else None
     rgb8_host = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory() if rank == 0 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
 
     def step(profile=False):
-        scene.render_tiles_device(w, h, tiles.data_ptr(), max_depth=md, rank=rank, world=world, stream=stream,
-                                  flags=rtp.RENDER_PROFILE if profile else 0)
-        if world > 1:
-            dist.gather(tiles, list(gathered.chunk(world)) if rank == 0 else None, dst=0)
-        if rank == 0:
-            src = gathered if world > 1 else tiles
-            scene.untile_device(w, h, world, src.data_ptr(), stride, d_rgb8=rgb8.data_ptr(), stream=stream)
+        mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None,
+                        flags=rtp.RENDER_PROFILE if profile else 0)
 
     def sync_all():
         if world > 1:

@@ -126,6 +126,14 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
  * device memory.  d_tiles: rtp_tile_buffer_bytes() bytes of device memory owned by the caller
  * (e.g. a torch tensor), stream: a cudaStream_t (NULL = default stream).  Asynchronous. */
 size_t rtp_tile_buffer_bytes(int width, int height, int rank, int world);
+/* Host-side description of the sharding (no device needed): the 32x32 screen tiles of the frame are
+ * numbered row-major (tile id = ty * tiles_x + tx, tiles_x = ceil(width / 32)); tile (tx, ty) belongs
+ * to rank (tx + ty) % world.  Fills tiles_of_rank (ids owned by `rank`, ascending - their order in
+ * the rank's tile-major buffer) and local_of_tile (for EVERY tile id, its index within its owner's
+ * buffer); either may be NULL.  Inside a tile, pixel (x, y) sits at float4 index
+ * ((y >> 2) * 4 + (x >> 3)) * 32 + (y & 3) * 8 + (x & 7)  (8x4-pixel warp footprints).
+ * Returns the number of tiles `rank` owns, or a negative rtp_status. */
+int rtp_tile_table(int width, int height, int rank, int world, int32_t *tiles_of_rank, int32_t *local_of_tile);
 int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tiles, void *stream,
                             rtp_stats *st);
 /* After the per-rank tile buffers have been gathered (NCCL) into d_all = [world][max tile

@@ -61,7 +61,7 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats"]
+           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats", "rtp_tile_table"]
 
 _lib = None
 
@@ -99,6 +99,7 @@ def lib():
         L.rtp_scene_get_boxes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rtp_scene_info.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
         L.rtp_frame_stats.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
+        L.rtp_tile_table.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -283,3 +284,14 @@ class Scene:
 
 def tile_buffer_bytes(w, h, rank=0, world=1):
     return lib().rtp_tile_buffer_bytes(w, h, rank, world)
+
+
+def tile_table(w, h, rank=0, world=1):
+    """(tile ids owned by `rank`, local index of every tile within its owner's buffer)."""
+    tx, ty = (w + TILE - 1) // TILE, (h + TILE - 1) // TILE
+    tiles = np.zeros(tx * ty, np.int32)
+    local = np.zeros(tx * ty, np.int32)
+    n = lib().rtp_tile_table(w, h, rank, world, tiles.ctypes.data, local.ctypes.data)
+    if n < 0:
+        raise RtpError(f"rtp error {n}: {lib().rtp_last_error().decode()}")
+    return tiles[:n], local

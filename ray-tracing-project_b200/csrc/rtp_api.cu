@@ -396,6 +396,15 @@ size_t rtp_tile_buffer_bytes(int width, int height, int rank, int world) {
   return (size_t)max_tile_count(width, height, world) * kTilePixels * sizeof(float4);
 }
 
+int rtp_tile_table(int width, int height, int rank, int world, int32_t *tiles_of_rank, int32_t *local_of_tile) {
+  if (width <= 0 || height <= 0 || world < 1 || rank < 0 || rank >= world) return fail(RTP_ERR_INVALID, "rtp_tile_table: bad argument");
+  std::vector<int32_t> tiles, local;
+  tile_tables(width, height, rank, world, tiles, local);
+  if (tiles_of_rank && !tiles.empty()) std::memcpy(tiles_of_rank, tiles.data(), tiles.size() * sizeof(int32_t));
+  if (local_of_tile && !local.empty()) std::memcpy(local_of_tile, local.data(), local.size() * sizeof(int32_t));
+  return (int)tiles.size();
+}
+
 int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tiles, void *stream, rtp_stats *st) {
   int rc = check_render_args(s, o);
   if (rc) return rc;
