@@ -82,7 +82,7 @@ def test_c4_shape_instanced_deep_bounces(rtp, po):
     base = dict(verts=g.verts, normals=g.normals, faces=g.faces, face_mat=g.face_mat, materials=g.materials, shape=g.shape)
     m = synth.instanced(base, 3, 3)
     assert len(m["faces"]) == 9 * 16311
-    view = synth.look_at((0.9, 0.7, 1.1), (0.0, -0.1, 0.0))
+    view = synth.look_at((0.55, 0.45, 0.7), (0.0, -0.1, 0.0))
     w, h = 640, 360
     s = rtp_scene(rtp, m)
     s.set_lights(synth.LIGHTS_C2, None)
@@ -95,7 +95,7 @@ def test_c4_shape_instanced_deep_bounces(rtp, po):
     px = np.stack([idx % w, idx // w], 1).astype(np.int32)
     o = po.render(pm, w, h, view=view, max_depth=6, point_lights=synth.LIGHTS_C2, pixels=px, threads=16)
     compare(out, o, px)
-    assert (out["hit"] >= 0).mean() > 0.2
+    assert (out["hit"] >= 0).mean() > 0.1
     assert out["stats"]["rays_reflection"] > 0
 
 
