@@ -77,6 +77,7 @@ struct rtp_scene {
   DevBuf<float4> nodes, tris, vnorm, boxes, materials, lights;
   DevBuf<int> face_of;
   DevBuf<int> counters;
+  DevBuf<int> park;  // parked-ray list of the trace kernels
   DeviceScene dS;
   DeviceCamera cam;
   bool have_camera = false, have_lights = false;
@@ -162,6 +163,7 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
   if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
   if ((e = s->counters.ensure(kCtrInts)) != cudaSuccess) return cleanup(e, "alloc counters");
+  if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
   // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
   std::vector<float4>().swap(h.nodes);
@@ -173,6 +175,16 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   std::memcpy(d.minv, h.minv, sizeof d.minv);
   d.n_tris = h.n_tris; d.n_nodes = h.n_nodes; d.n_boxes = h.n_boxes;
   query_launch_cfg(device, s->cfg);
+  constexpr int kParkCap = 1 << 17;  // 131072 parked rays (36 MiB); a full list only means no more parking
+  if ((e = s->park.ensure((size_t)kParkCap * kParkSlotBytes / sizeof(int))) != cudaSuccess) return cleanup(e, "alloc parked-ray list");
+  s->cfg.park_slots = s->park.p;
+  s->cfg.park_cap = kParkCap;
+  {
+    int l2 = 0;
+    cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device);
+    const size_t scene_bytes = ((size_t)h.n_nodes + (size_t)h.n_tris) * 64;
+    s->cfg.scene_exceeds_l2 = scene_bytes > (size_t)(l2 > 0 ? l2 : (64 << 20)) / 2;
+  }
   if ((e = cudaGetLastError()) != cudaSuccess) return cleanup(e, "query_launch_cfg");
   *out = s;
   return RTP_OK;
@@ -503,6 +515,7 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
   cudaStream_t cs = (cudaStream_t)stream;
   int *cursor = s->counters.p + kCtrAux;
   CK(cudaMemsetAsync(cursor, 0, sizeof(int), cs));
+  CK(cudaMemsetAsync(s->counters.p + kCtrPark + 2 * 16, 0, 2 * sizeof(int), cs));
   if (st) CK(cudaEventRecord(s->ev[0], cs));
   if (mode == RTP_RAYS_CLOSEST) {
     if (!d_face) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: face output required");

@@ -32,6 +32,7 @@ namespace rtp {
 
 constexpr int kStackSize = 64;
 constexpr int kSentinel = 0x7fffffff;
+constexpr int kMaxNodesPerStep = 32;
 constexpr unsigned kTriFlagNormalCheck = 0x80000000u;  // vertex normals may cancel: run the Q12 check
 constexpr unsigned kTriMatMask = 0x0000ffffu;
 constexpr int kMaxDepth = 8;   // direct-colour slots per pixel
@@ -67,6 +68,16 @@ struct DeviceCamera {
 #endif
 
 RTP_HD v3 xyz(float4 a) { return mk3(a.x, a.y, a.z); }
+
+// Traversal work counters: compiled in only for tests/hostsim (CPU, -DRTP_TRAV_STATS), where they
+// give nodes / leaves / triangle tests per ray for the roofline discussion in DESIGN.md.
+#if defined(RTP_TRAV_STATS) && !defined(__CUDA_ARCH__)
+struct TravStats { long long nodes, leaves, tris, careful; };
+extern thread_local TravStats g_trav_stats;
+#define RTP_STAT(x) (++g_trav_stats.x)
+#else
+#define RTP_STAT(x) ((void)0)
+#endif
 
 // ---- Camera::screenToWorld + direction (camera.hpp:155-173, flyscene.cpp:308) ----------------
 RTP_HD v3 primary_dir(const DeviceCamera &c, int i, int j) {
@@ -187,11 +198,15 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
 //                    that test fails.  The unfiltered minimum, when its box passes, is also the
 //                    filtered minimum.  A runtime flag (not a second instantiation) keeps the whole
 //                    traversal state in registers: no out-of-line re-trace function.
+// A step visits at most kMaxNodesPerStep inner nodes (it is resumable: t.node = the next inner node),
+// so that a ray with a long leaf-free stretch - an unoccluded shadow ray - still comes back to the
+// caller, who may hand a straggler to the whole warp (rtp_kernels.cu).
 template <bool ANY>
 RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
   int node = t.node, sp = t.sp;
-  while (node >= 0 && node != kSentinel) {
+  for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
+    RTP_STAT(nodes);
     float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
     float c0lox = fmaf(n0.x, t.idx, -t.oodx), c0hix = fmaf(n0.y, t.idx, -t.oodx);
     float c0loy = fmaf(n0.z, t.idy, -t.oody), c0hiy = fmaf(n0.w, t.idy, -t.oody);
@@ -218,7 +233,9 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
   while (node < 0) {
     int enc = ~node;
     int first = enc >> 3, cnt = (enc & 7) + 1;
+    RTP_STAT(leaves);
     for (int k = 0; k < cnt; ++k) {
+      RTP_STAT(tris);
       float tt;
       float4 T0, T1;
       if (!tri_exact(S, first + k, t.o, t.d, t.tbest, tt, T0, T1)) continue;
@@ -249,6 +266,7 @@ RTP_HD bool closest_needs_rerun(const DeviceScene &S, Trav &t, int *stack) {
   const v3 o = t.o, d = t.d;
   trav_init(t, o, d, stack);
   t.careful = true;
+  RTP_STAT(careful);
   return true;
 }
 

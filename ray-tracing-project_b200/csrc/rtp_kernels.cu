@@ -128,18 +128,151 @@ __device__ __forceinline__ bool RaysClosest::finish(int q, Trav &t, int *stack) 
   return true;
 }
 
+// ---- stragglers: step budget, parking list, warp-cooperative traversal (k_coop) ------------------
+// A ray that is still running when every other lane of its warp has finished is a chain of
+// dependent node fetches (a cold node costs a DRAM round trip, ~0.6 us on B200) executed by one lane
+// while 31 sit idle; a single 650-node ray used to set the duration of the whole closest-hit kernel,
+// and the max-of-32 last batches that of the shadow kernel (profiles/r01_tail.md).
+//
+// k_trace therefore PARKS stragglers: when a warp has spent more than a budget of steps on its rays
+// and only a few lanes still hold one, those rays - id, best hit so far, pending traversal stack -
+// are appended to a global list and the lanes are free.  k_coop, launched right behind, finishes
+// every parked ray with a whole warp (coop_trace): a shared-memory stack, every iteration the 32
+// lanes pop up to 32 entries, test them in parallel (inner node: both child slabs; leaf: the exact
+// triangle tests) and push the surviving children back, the near child of the top entry last (a
+// 32-wide speculative depth-first order).  Candidates merge through a lexicographic (t, reference
+// rank) warp minimum - exactly the order-independent rule of trav_step - so the result is the one
+// the serial traversal gives.
+// (Tried first and dropped: finishing parked rays inside k_trace.  A shared ring polled by idle
+// warps made every reservation cost 10-70 us; an in-kernel call or inlined copy of coop_trace pushed
+// the node loop of trav_step into local-memory spills at 64 registers, -25 % on the whole frame.)
+constexpr int kCoopSoft = 160;                             // above this fill level only one entry is popped per iteration
+constexpr int kCoopStack = kCoopSoft + kStackSize + 32;    // depth-first growth bound + slack
+constexpr int kParkInts = 5 + kStackSize + 3;              // (ray id + 1) | careful << 31, tbest, rank, slot, n, entries
+static_assert(kParkInts * sizeof(int) == kParkSlotBytes, "parked-ray slot size");
+
+struct ParkList {
+  int *slots;   // kParkInts ints per parked ray
+  int *ctr;     // [0] rays parked by k_trace, [1] k_coop's cursor (zeroed per frame, one pair per launch)
+  int cap;      // slots available; a ray that finds the list full simply carries on
+  int budget;   // steps a warp spends on a batch before its last lanes count as stragglers (huge = never park)
+  int lanes;    // ... and at most this many lanes still hold a ray
+};
+
+// Finishes the (warp-uniform) ray in t with all 32 lanes, starting from the n pending entries in ws;
+// t.tbest/rbest/sbest hold the best hit found so far on entry and the final one on return.
+template <bool ANY>
+__device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const v3 bo, int *ws, int n) {
+  const int lane = threadIdx.x & 31;
+  const unsigned gt = lane == 31 ? 0u : (kFull << (lane + 1));  // lanes above this one
+  const float idx = t.idx, idy = t.idy, idz = t.idz, oodx = t.oodx, oody = t.oody, oodz = t.oodz;
+  const v3 o = t.o, d = t.d;
+  const bool careful = t.careful;
+  float tb = t.tbest;
+  unsigned rb = t.rbest;
+  int sb = t.sbest;
+  while (n > 0) {
+    const int room = kCoopSoft - n;
+    const int k = min(min(32, n), room > 1 ? room : 1);
+    const int my = lane < k ? ws[n - 1 - lane] : kSentinel;  // lane 0 takes the top of the stack
+    n -= k;
+    __syncwarp();
+    int push_far = kSentinel, push_near = kSentinel;
+    bool improved = false;
+    if (lane < k) {
+      if (my >= 0) {
+        const float4 *Np = S.nodes + 4 * (size_t)my;
+        const float4 n0 = __ldg(Np), n1 = __ldg(Np + 1), n2 = __ldg(Np + 2), n3 = __ldg(Np + 3);
+        const float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
+        const float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
+        const float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
+        const float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
+        const float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
+        const float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
+        const float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)), fmaxf(fminf(c0loz, c0hiz), 0.f));
+        const float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)), fminf(fmaxf(c0loz, c0hiz), tb));
+        const float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)), fmaxf(fminf(c1loz, c1hiz), 0.f));
+        const float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)), fminf(fmaxf(c1loz, c1hiz), tb));
+        const bool h0 = c0min <= c0max, h1 = c1min <= c1max;
+        const int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
+        if (h0 && h1) {
+          const bool swap = c1min < c0min;
+          push_near = swap ? ch1 : ch0;
+          push_far = swap ? ch0 : ch1;
+        } else if (h0 || h1) {
+          push_near = h0 ? ch0 : ch1;
+        }
+      } else {
+        const int enc = ~my;
+        const int first = enc >> 3, cnt = (enc & 7) + 1;
+        for (int j = 0; j < cnt; ++j) {
+          float tt;
+          float4 T0, T1;
+          if (!tri_exact(S, first + j, o, d, tb, tt, T0, T1)) continue;
+          const unsigned rank = (unsigned)f2i(T0.w);
+          if (!ANY && !(tt < tb || (sb >= 0 && rank < rb))) continue;
+          if ((ANY || careful) && !ref_box_pass(S, bo, d, f2i(T1.w))) continue;
+          tb = ANY ? tb : tt;
+          rb = rank;
+          sb = first + j;
+          improved = true;
+          if (ANY) break;
+        }
+      }
+    }
+    const unsigned found = __ballot_sync(kFull, improved);
+    if (found) {
+      if constexpr (ANY) {
+        sb = __shfl_sync(kFull, sb, __ffs(found) - 1);
+        break;
+      } else {
+#pragma unroll
+      for (int m = 16; m > 0; m >>= 1) {  // lexicographic (t, rank) minimum; every lane started from the warp's best
+        const float t2 = __shfl_xor_sync(kFull, tb, m);
+        const unsigned r2 = __shfl_xor_sync(kFull, rb, m);
+        const int s2 = __shfl_xor_sync(kFull, sb, m);
+        if (s2 >= 0 && (sb < 0 || t2 < tb || (t2 == tb && r2 < rb))) { tb = t2; rb = r2; sb = s2; }
+      }
+      }
+    }
+    const bool pf = push_far != kSentinel, pn = push_near != kSentinel;
+    const unsigned bf = __ballot_sync(kFull, pf), bn = __ballot_sync(kFull, pn);
+    const int pos = n + __popc(bf & gt) + __popc(bn & gt);  // entries of higher lanes go below
+    if (pf) ws[pos] = push_far;
+    if (pn) ws[pos + (pf ? 1 : 0)] = push_near;
+    n += __popc(bf) + __popc(bn);
+    __syncwarp();
+  }
+  __syncwarp();
+  t.tbest = tb; t.rbest = rb; t.sbest = sb;
+  t.node = kSentinel; t.sp = 0;
+}
+
 // ---- the persistent trace kernel -----------------------------------------------------------------
 #ifndef RTP_TRACE_MINB
 #define RTP_TRACE_MINB 8
 #endif
+#ifdef RTP_TRACE_TIMING  // debug builds only (scratch A/B runs): per-warp start / end / last-fetch times
+__device__ unsigned long long g_warp_timing[2 * 8192 * 8];
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
 template <class Job, int kRefillBelow>
-__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job) {
+__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, const ParkList pl) {
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
   const int count = job.count();
+#ifdef RTP_TRACE_TIMING
+  const unsigned long long tm_start = gtime();
+  unsigned long long tm_fetch = tm_start;
+  unsigned tm_nb = 0, tm_nc = 0;
+#endif
   int stack[kStackSize];
   Trav t;
-  int q = 0;
+  int q = 0, age = 0;  // age: steps since this warp last took rays (warp-uniform)
   bool have = false, exhausted = false;
   for (;;) {
     unsigned act = __ballot_sync(kFull, have);
@@ -152,17 +285,90 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job) {
       if (lane == leader) base = atomicAdd(job.cursor, n_need);
       base = __shfl_sync(kFull, base, leader);
       exhausted = base + n_need >= count;
+#ifdef RTP_TRACE_TIMING
+      if (base < count) { tm_fetch = gtime(); ++tm_nb; }
+#endif
       if (!have) {
         q = base + __popc(need & lt);
         if (q < count) have = job.init(q, t, stack);
       }
       act = __ballot_sync(kFull, have);
+      age = 0;
     }
     if (act == 0) {
       if (exhausted) break;
       continue;
     }
+    if (++age > pl.budget && __popc(act) <= pl.lanes) {
+      // only stragglers are left in this warp: park them for k_coop
+      if (have) {
+        const int at = atomicAdd(pl.ctr, 1);
+        if (at < pl.cap) {
+          int *e = pl.slots + (size_t)at * kParkInts;
+          e[0] = (q + 1) | (t.careful ? (int)0x80000000 : 0);
+          e[1] = f2i(t.tbest);
+          e[2] = (int)t.rbest;
+          e[3] = t.sbest;
+          int n = 0;
+          for (int i = 1; i <= t.sp; ++i) e[5 + n++] = stack[i];
+          if (t.node != kSentinel) e[5 + n++] = t.node;
+          e[4] = n;
+          have = false;
+#ifdef RTP_TRACE_TIMING
+          ++tm_nc;
+#endif
+        }
+      }
+      age = 0;
+      continue;
+    }
     if (have && trav_step<Job::kAny>(job.S, t, stack, job.box_origin(q, t))) have = !job.finish(q, t, stack);
+  }
+#ifdef RTP_TRACE_TIMING
+  if (lane == 0) {
+    const unsigned wid = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (wid < 8192) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      unsigned long long *o = g_warp_timing + ((Job::kAny ? 8192 : 0) + wid) * 8;
+      o[0] = tm_start; o[1] = gtime(); o[2] = tm_fetch - tm_start;
+      o[3] = smid | ((unsigned long long)tm_nb << 16) | ((unsigned long long)tm_nc << 32);
+      o[4] = 0; o[5] = 0; o[6] = 0; o[7] = 0;
+    }
+  }
+#endif
+}
+
+// Finishes the rays k_trace parked, one warp per ray.
+template <class Job>
+__global__ void __launch_bounds__(128, 4) k_coop(const Job job, const ParkList pl) {
+  __shared__ int s_ws[4][kCoopStack];
+  int *const ws = s_ws[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const int n_parked = min(*pl.ctr, pl.cap);
+  int stack[1];  // job.finish -> closest_needs_rerun -> trav_init writes stack[0] only
+  for (;;) {
+    int k = 0;
+    if (lane == 0) k = atomicAdd(pl.ctr + 1, 1);
+    k = __shfl_sync(kFull, k, 0);
+    if (k >= n_parked) break;
+    const int *e = pl.slots + (size_t)k * kParkInts;
+    const int ex = e[0];
+    const int q = (ex & 0x7fffffff) - 1;
+    Trav t;
+    job.init(q, t, stack);  // the same ray in every lane
+    t.tbest = i2f(e[1]); t.rbest = (unsigned)e[2]; t.sbest = e[3]; t.careful = ex < 0;
+    int n = e[4];
+    for (int i = lane; i < n; i += 32) ws[i] = e[5 + i];
+    __syncwarp();
+    for (;;) {
+      coop_trace<Job::kAny>(job.S, t, job.box_origin(q, t), ws, n);
+      if (job.finish(q, t, stack)) break;
+      if (lane == 0) ws[0] = 0;  // closest-hit: the winner's box failed - start over from the root, careful
+      n = 1;
+      __syncwarp();
+    }
+    __syncwarp();
   }
 }
 
@@ -325,6 +531,13 @@ __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_s
 }
 
 int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning runs)
+// Straggler policy (measured on B200, profiles/r01_tail.md): parking pays for closest-hit launches on
+// scenes that do not fit the L2 (cold nodes make the serial chain slow: C3 closest-hit 0.47 -> 0.40 ms);
+// on L2-resident scenes and for shadow rays k_coop's launch costs more than the shorter tail saves.
+int g_budget = 12;      // RTP_BUDGET: steps before the last lanes of a warp count as stragglers (0: never park)
+int g_park_lanes = 4;   // RTP_PARK_LANES: ... when at most this many lanes are left
+int g_park_any = 0;     // RTP_PARK_ANY=1: park shadow rays too
+int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
 
 // Refill policy: a warp refills its idle lanes from the global ray list when fewer than `refill`
 // lanes still hold a ray.  Coherent waves (camera rays, their point-light shadow rays) run
@@ -332,16 +545,30 @@ int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning 
 // together, measured +6% on C3); scattered waves (reflection levels, caller-supplied rays)
 // keep at least 24 lanes busy.
 template <class Job>
-void launch_trace(const Job &job, int blocks, int threads, bool coherent, cudaStream_t st) {
+void launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters, int launch_slot, bool coherent,
+                  cudaStream_t st) {
+  const int threads = cfg.threads;
   if (g_refill == -2) {
     const char *e = std::getenv("RTP_REFILL");
     g_refill = e ? std::atoi(e) : -1;
+    if ((e = std::getenv("RTP_BUDGET"))) g_budget = std::atoi(e);
+    if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = std::atoi(e);
+    if ((e = std::getenv("RTP_PARK_ANY"))) g_park_any = std::atoi(e);
+    if ((e = std::getenv("RTP_PARK_SMALL"))) g_park_small = std::atoi(e);
   }
   const int refill = g_refill >= 0 ? g_refill : (coherent ? 1 : 24);
-  if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job);
-  else if (refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job);
-  else if (refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job);
-  else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job);
+  ParkList pl;
+  pl.slots = cfg.park_slots;
+  pl.ctr = counters + kCtrPark + 2 * launch_slot;
+  pl.cap = cfg.park_cap;
+  const bool park = g_budget > 0 && cfg.park_slots && (!Job::kAny || g_park_any) && (cfg.scene_exceeds_l2 || g_park_small);
+  pl.budget = park ? g_budget : 0x3fffffff;
+  pl.lanes = g_park_lanes;
+  if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job, pl);
+  else if (refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job, pl);
+  else if (refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
+  else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job, pl);
+  if (pl.budget < 0x3fffffff) k_coop<Job><<<cfg.blocks_coop, 128, 0, st>>>(job, pl);
 }
 
 }  // namespace
@@ -354,6 +581,7 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny, 24>, cfg.threads, 0);
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
+  cfg.blocks_coop = sms * 2;
 }
 
 void launch_raygen(const FrameParams &p, cudaStream_t st) { k_raygen<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
@@ -369,7 +597,7 @@ void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaS
   j.cursor = p.counters + kCtrFetchClosest + depth;
   j.count_ptr = depth == 0 ? nullptr : p.counters + kCtrPaths + depth;
   j.count_fixed = p.n_px;
-  launch_trace(j, cfg.blocks_closest, cfg.threads, depth == 0 && !p.user_rays, st);
+  launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, st);
 }
 
 void launch_prep(const FrameParams &p, int depth, cudaStream_t st) {
@@ -383,7 +611,7 @@ void launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaSt
   j.occl = p.occl;
   j.cursor = p.counters + kCtrFetchAny + depth;
   j.hits_ptr = p.counters + kCtrHits + depth;
-  launch_trace(j, cfg.blocks_any, cfg.threads, depth == 0 && !p.user_rays, st);
+  launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, st);
 }
 
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
@@ -404,14 +632,20 @@ void launch_rays_closest(const DeviceScene &S, const float *rays, long long n, i
                          const LaunchCfg &cfg, cudaStream_t st) {
   RaysClosest j;
   j.S = S; j.rays = rays; j.face = face; j.tout = t; j.cursor = cursor; j.n = (int)n;
-  launch_trace(j, cfg.blocks_closest, cfg.threads, false, st);
+  launch_trace(j, cfg.blocks_closest, cfg, cursor - kCtrAux, 16, false, st);
 }
 
 void launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st) {
   RaysAny j;
   j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
-  launch_trace(j, cfg.blocks_any, cfg.threads, false, st);
+  launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, st);
 }
 
 }  // namespace rtp
+
+#ifdef RTP_TRACE_TIMING
+extern "C" int rtp_debug_timing(unsigned long long *out) {
+  return (int)cudaMemcpyFromSymbol(out, rtp::g_warp_timing, sizeof(unsigned long long) * 2 * 8192 * 8);
+}
+#endif

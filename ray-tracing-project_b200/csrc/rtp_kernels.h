@@ -12,7 +12,10 @@ constexpr int kCtrHits = 16;          // [depth] hits found at depth
 constexpr int kCtrFetchClosest = 32;  // [depth] persistent-warp ray cursor of k_closest
 constexpr int kCtrFetchAny = 48;      // [depth] persistent-warp ray cursor of k_anyhit
 constexpr int kCtrAux = 62;           // ray-batch API cursor
-constexpr int kCtrInts = 64;
+constexpr int kCtrPark = 64;          // parked-ray list, 2 ints per trace launch of a frame ([depth] closest,
+                                      // [8 + depth] any-hit, [16] ray-batch API): rays parked, k_coop cursor
+constexpr int kCtrInts = kCtrPark + 2 * 17 + 2;
+constexpr int kParkSlotBytes = 288;   // one parked ray (rtp_kernels.cu: kParkInts)
 
 struct FrameParams {
   DeviceScene S;
@@ -40,7 +43,10 @@ struct FrameParams {
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_any = 0, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, threads = 128;
+  int *park_slots = nullptr;  // parked-ray list storage (park_cap * kParkSlotBytes), owned by the scene
+  int park_cap = 0;
+  bool scene_exceeds_l2 = false;  // nodes + triangles larger than half the L2: traversal chains run on cold lines
 };
 void query_launch_cfg(int device, LaunchCfg &cfg);
 

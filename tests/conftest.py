@@ -77,7 +77,7 @@ def hostsim():
                                                                       ("scene_host.cpp", "bvh_build.cpp", "ref_boxes.cpp")]
     deps = srcs + glob.glob(os.path.join(csrc, "*.h"))
     if not os.path.exists(HOSTSIM) or any(os.path.getmtime(d) > os.path.getmtime(HOSTSIM) for d in deps):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared",
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-DRTP_TRAV_STATS",
                                "-I/usr/local/cuda/include", "-o", HOSTSIM] + srcs + ["-lpthread"])
     H = C.CDLL(HOSTSIM)
     H.hostsim_create.restype = C.c_char_p

@@ -15,6 +15,7 @@
 #include "../../ray-tracing-project_b200/csrc/scene_host.h"
 
 using namespace rtp;
+namespace rtp { thread_local TravStats g_trav_stats; }
 
 extern "C" {
 
@@ -132,6 +133,44 @@ void hostsim_rays(hostsim_scene *s, const float *rays, long long n, int anyhit, 
       out[k] = slot >= 0 ? s->d.face_of[slot] : -1;
       if (t) t[k] = tt;
     }
+  }
+}
+
+// per primary ray: nodes visited, leaves visited, triangles tested, careful re-runs (out: n x 4)
+void hostsim_trav_stats(hostsim_scene *s, const rtp_camera *c, const int *pixels, long long n, int *out) {
+  DeviceCamera cam;
+  derive_camera(*c, cam);
+  for (long long k = 0; k < n; ++k) {
+    v3 o = mk3(cam.eye[0], cam.eye[1], cam.eye[2]);
+    v3 d = primary_dir(cam, pixels[2 * k], pixels[2 * k + 1]);
+    g_trav_stats = TravStats{0, 0, 0, 0};
+    float t; int slot;
+    traverse<false>(s->d, o, d, o, t, slot);
+    out[4 * k] = (int)g_trav_stats.nodes; out[4 * k + 1] = (int)g_trav_stats.leaves;
+    out[4 * k + 2] = (int)g_trav_stats.tris; out[4 * k + 3] = (int)g_trav_stats.careful;
+  }
+}
+// same for the shadow ray of light 0 from each primary hit (out: n x 4, last column: 1 = occluded, -1 = no hit)
+void hostsim_shadow_stats(hostsim_scene *s, const rtp_camera *c, const int *pixels, long long n, int *out) {
+  DeviceCamera cam;
+  derive_camera(*c, cam);
+  const DeviceScene &S = s->d;
+  for (long long k = 0; k < n; ++k) {
+    v3 o = mk3(cam.eye[0], cam.eye[1], cam.eye[2]);
+    v3 d = primary_dir(cam, pixels[2 * k], pixels[2 * k + 1]);
+    float t; int slot;
+    traverse<false>(S, o, d, o, t, slot);
+    out[4 * k] = out[4 * k + 1] = out[4 * k + 2] = 0; out[4 * k + 3] = -1;
+    if (slot < 0 || S.n_lights < 1) continue;
+    v3 P = vadd(o, vmuls(d, t));
+    float4 l0 = S.lights[0];
+    v3 L = xyz(l0);
+    if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));
+    g_trav_stats = TravStats{0, 0, 0, 0};
+    float ts; int ss;
+    bool occ = traverse<true>(S, vadd(P, vmuls(L, (float)0.003)), L, P, ts, ss);
+    out[4 * k] = (int)g_trav_stats.nodes; out[4 * k + 1] = (int)g_trav_stats.leaves;
+    out[4 * k + 2] = (int)g_trav_stats.tris; out[4 * k + 3] = occ ? 1 : 0;
   }
 }
 
