@@ -68,43 +68,60 @@ def build_workload(name, synth):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md).  Sampled in-process
+    through NVML every few ms (the timed region of the default run is well under a second, too short
+    for `nvidia-smi -lms`); falls back to one nvidia-smi query when NVML is unavailable."""
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
 
     def __init__(self, gpu_index):
-        self.rows, self.proc, self.gpu = [], None, gpu_index
+        self.rows, self.gpu, self.stop_flag, self.th, self.h, self.nv = [], gpu_index, False, None, None, None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            threading.Thread(target=self._read, daemon=True).start()
-        except OSError:
-            self.proc = None
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.gpu]) if vis and vis.split(",")[self.gpu].strip().isdigit() else self.gpu
+            self.h, self.nv = pynvml.nvmlDeviceGetHandleByIndex(idx), pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+            return
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([time.perf_counter()] + [x.strip() for x in line.split(",")])
-
-    def stop(self, t_begin=None, t_end=None):
-        if self.proc:
-            self.proc.terminate()
+    def _run(self):
+        nv = self.nv
+        while not self.stop_flag:
             try:
-                self.proc.wait(timeout=5)
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+                    else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                self.rows.append((time.perf_counter(), float(mhz), int(reasons)))
             except Exception:
                 pass
-        rows = [r[1:] for r in self.rows if len(r) >= 7 and (t_begin is None or t_begin <= r[0] <= t_end)]
-        if not rows:  # region shorter than one sampling period: fall back to everything we saw
-            rows = [r[1:] for r in self.rows if len(r) >= 7]
-        num = lambda x: x.replace(".", "", 1).isdigit()
-        sm = [float(r[0]) for r in rows if num(r[0])]
-        mx = [float(r[1]) for r in rows if num(r[1])]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in rows for i in range(4) if r[2 + i].lower() == "active"})
-        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
-                    reasons=reasons, samples=len(sm))
+            time.sleep(0.004)
+
+    def stop(self, t_begin=None, t_end=None):
+        self.stop_flag = True
+        if self.th:
+            self.th.join(timeout=2)
+        if self.h is None:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=clocks.sm,clocks.max.sm",
+                                      "--format=csv,noheader,nounits"], stdout=subprocess.PIPE, text=True, timeout=20).stdout
+                a, b = [float(x) for x in out.strip().split(",")]
+                return dict(sm_mhz=a, sm_max_mhz=b, reasons=[], samples=1, how="nvidia-smi after the timed region (NVML unavailable)")
+            except Exception:
+                return dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
+        rows = [r for r in self.rows if t_begin is None or t_begin <= r[0] <= t_end] or self.rows
+        sm = [r[1] for r in rows]
+        mask = 0
+        for r in rows:
+            mask |= r[2]
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=self.max_mhz,
+                    reasons=sorted(k for k, bit in self.BAD.items() if mask & bit), samples=len(sm),
+                    how="NVML, 4 ms period, samples inside the timed region")
 
 
 def cpu_baseline_port(wl, n_rays_target=None, seconds=15.0):
@@ -265,7 +282,7 @@ def run_ours(args, wl, rtp):
         k_any.append(fs["ms_anyhit"])
         k_shade.append(fs["ms_shade"])
     clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
-    launches_rank0 = (4 * md + 2 + 1) * args.steps  # raygen + 4 per level + resolve + untile
+    launches_rank0 = (fs["kernel_launches"] + (1 if rank == 0 else 0)) * args.steps  # frame kernels + untile on rank 0
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
     e2e_ms = []

@@ -334,11 +334,11 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   };
   CK(mark(2)); launch_raygen(p, st); ++n;
   for (int d = 0; d < p.max_depth; ++d) {
-    CK(mark(0)); launch_closest(p, d, s->cfg, st);
+    CK(mark(0)); n += launch_closest(p, d, s->cfg, st);
     CK(mark(2)); launch_prep(p, d, st);
-    CK(mark(1)); launch_anyhit(p, d, s->cfg, st);
+    CK(mark(1)); n += launch_anyhit(p, d, s->cfg, st);
     CK(mark(2)); launch_accum(p, d, st);
-    n += 4;
+    n += 2;
   }
   CK(mark(2)); launch_resolve(p, st); ++n;
   CK(mark(-1));
@@ -517,12 +517,13 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
   CK(cudaMemsetAsync(cursor, 0, sizeof(int), cs));
   CK(cudaMemsetAsync(s->counters.p + kCtrPark + 2 * 16, 0, 2 * sizeof(int), cs));
   if (st) CK(cudaEventRecord(s->ev[0], cs));
+  int launches = 0;
   if (mode == RTP_RAYS_CLOSEST) {
     if (!d_face) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: face output required");
-    launch_rays_closest(s->dS, (const float *)d_rays, n, (int *)d_face, (float *)d_t, cursor, s->cfg, cs);
+    launches = launch_rays_closest(s->dS, (const float *)d_rays, n, (int *)d_face, (float *)d_t, cursor, s->cfg, cs);
   } else if (mode == RTP_RAYS_ANYHIT) {
     if (!d_occluded) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: occluded output required");
-    launch_rays_anyhit(s->dS, (const float *)d_rays, n, (unsigned char *)d_occluded, cursor, s->cfg, cs);
+    launches = launch_rays_anyhit(s->dS, (const float *)d_rays, n, (unsigned char *)d_occluded, cursor, s->cfg, cs);
   } else {
     return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: mode must be CLOSEST or ANYHIT");
   }
@@ -533,7 +534,7 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
     std::memset(st, 0, sizeof *st);
     CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
     st->ms_total = st->ms_trace;
-    st->kernel_launches = 1;
+    st->kernel_launches = launches;
     (mode == RTP_RAYS_ANYHIT ? st->rays_shadow : st->rays_primary) = n;
     st->n_bvh_nodes = s->host.n_nodes;
     st->n_triangles = s->host.n_tris;

@@ -545,8 +545,8 @@ int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
 // together, measured +6% on C3); scattered waves (reflection levels, caller-supplied rays)
 // keep at least 24 lanes busy.
 template <class Job>
-void launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters, int launch_slot, bool coherent,
-                  cudaStream_t st) {
+int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters, int launch_slot, bool coherent,
+                 cudaStream_t st) {
   const int threads = cfg.threads;
   if (g_refill == -2) {
     const char *e = std::getenv("RTP_REFILL");
@@ -568,7 +568,9 @@ void launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counter
   else if (refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job, pl);
   else if (refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
   else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job, pl);
-  if (pl.budget < 0x3fffffff) k_coop<Job><<<cfg.blocks_coop, 128, 0, st>>>(job, pl);
+  if (pl.budget >= 0x3fffffff) return 1;
+  k_coop<Job><<<cfg.blocks_coop, 128, 0, st>>>(job, pl);
+  return 2;
 }
 
 }  // namespace
@@ -586,7 +588,7 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
 
 void launch_raygen(const FrameParams &p, cudaStream_t st) { k_raygen<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
 
-void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
   FrameClosest j;
   j.S = p.S;
   j.ro = p.ray_o[depth & 1];
@@ -597,21 +599,21 @@ void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaS
   j.cursor = p.counters + kCtrFetchClosest + depth;
   j.count_ptr = depth == 0 ? nullptr : p.counters + kCtrPaths + depth;
   j.count_fixed = p.n_px;
-  launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, st);
+  return launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, st);
 }
 
 void launch_prep(const FrameParams &p, int depth, cudaStream_t st) {
   k_prep<<<(p.n_px + 255) / 256, 256, 0, st>>>(p, depth);
 }
 
-void launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
   FrameAny j;
   j.S = p.S;
   j.pbuf = p.pbuf;
   j.occl = p.occl;
   j.cursor = p.counters + kCtrFetchAny + depth;
   j.hits_ptr = p.counters + kCtrHits + depth;
-  launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, st);
+  return launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, st);
 }
 
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
@@ -628,18 +630,18 @@ void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of
                                                         world, only_rank, rgb, rgb8, hit);
 }
 
-void launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
+int launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
                          const LaunchCfg &cfg, cudaStream_t st) {
   RaysClosest j;
   j.S = S; j.rays = rays; j.face = face; j.tout = t; j.cursor = cursor; j.n = (int)n;
-  launch_trace(j, cfg.blocks_closest, cfg, cursor - kCtrAux, 16, false, st);
+  return launch_trace(j, cfg.blocks_closest, cfg, cursor - kCtrAux, 16, false, st);
 }
 
-void launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
+int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st) {
   RaysAny j;
   j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
-  launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, st);
+  return launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, st);
 }
 
 }  // namespace rtp

@@ -52,12 +52,13 @@ void query_launch_cfg(int device, LaunchCfg &cfg);
 
 // depth-0 rays of every owned pixel (traceRayThread, flyscene.cpp:299-314) or the caller's rays
 void launch_raygen(const FrameParams &p, cudaStream_t st);
-// calculateMinimumFace for every ray of `depth` (flyscene.cpp:373-396)
-void launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// calculateMinimumFace for every ray of `depth` (flyscene.cpp:373-396); returns the kernels launched
+// (k_trace, plus k_coop when stragglers are parked)
+int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
 // per hit: P, interpolated normal, compaction (flyscene.cpp:464,572-600)
 void launch_prep(const FrameParams &p, int depth, cudaStream_t st);
 // shadow() for every (hit, light) pair (flyscene.cpp:510-526)
-void launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
 // calcSingleColor / calculateColor + reflection-ray spawn (flyscene.cpp:542-566,603-614,355-363)
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st);
 // fold-back of the per-depth colours (flyscene.cpp:366-370) -> tile-major framebuffer
@@ -68,9 +69,9 @@ void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of
                    int world, int only_rank, float *rgb, unsigned char *rgb8, int *hit, cudaStream_t st);
 
 // ray-batch API (rtp_trace_rays): rays = n x (o, d) floats on the device
-void launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
+int launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
                          const LaunchCfg &cfg, cudaStream_t st);
-void launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
+int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st);
 
 }  // namespace rtp
