@@ -18,6 +18,9 @@ Workloads (BASELINE.json configs; --workload):
   c2           shipped default scene (dodgeColorTest, 16 311 triangles), 1920x1080, 4 lights,
                max_depth 4 (reflection depth 3)
   c1           plane.obj, 256x256, 1 light, max_depth 2
+  c4           dodgeColorTest instanced 25x25 = 10 194 375 triangles, 3840x2160, 4 lights, max_depth 6
+  c5           incoherent stress: 64 ambient-occlusion rays per pixel of the C3 frame (any-hit queries
+               through rtp_trace_rays_device), rays sharded over the GPUs
 """
 import argparse
 import importlib
@@ -64,6 +67,19 @@ def build_workload(name, synth):
         m = load_golden_mesh("plane")
         return dict(mesh=m, w=256, h=256, max_depth=2, lights=synth.LIGHT_DEFAULT, view=None,
                     desc="C1: plane.obj (2 triangles), 256x256, 1 point light, max_depth 2, default camera")
+    if name == "c4":
+        m = synth.instanced(load_golden_mesh("dodgeColorTest"), 25, 25)
+        return dict(mesh=m, w=3840, h=2160, max_depth=6, lights=synth.LIGHTS_C2,
+                    view=synth.look_at((0.55, 0.45, 0.7), (0.0, -0.1, 0.0)),
+                    desc="C4: dodgeColorTest.obj instanced 25x25 = 10194375 triangles, 3840x2160, 4 point lights, "
+                         "max_depth 6 (reflection depth 5), camera eye (.55,.45,.7) -> (0,-.1,0)")
+    if name == "c5":
+        m = synth.terrain(708)
+        return dict(mesh=m, w=1920, h=1080, max_depth=1, lights=synth.LIGHT_DEFAULT, ao=64, eye=(0.0, 0.30, 0.20),
+                    view=synth.look_at((0.0, 0.30, 0.20), (0.0, -0.05, -0.08)),
+                    desc="C5: incoherent stress on the C3 terrain (1002528 triangles): from every primary hit of the "
+                         "1920x1080 frame 64 directions uniform on the hemisphere around the face normal "
+                         "(Philox, seed 1234), any-hit queries (= Flyscene::shadow)")
     raise SystemExit(f"unknown workload {name}")
 
 
@@ -235,15 +251,30 @@ def run_ours(args, wl, rtp):
     scene.set_camera(w, h, wl["view"])
     info = scene.info()
     mg = importlib.import_module("ray-tracing-project_b200.multigpu")
+    # the frame lands in GPU 0's image: --gather peer (default) = every rank's resolve kernel stores its
+    # tiles there over NVLink (CUDA IPC), --gather nccl = tile buffers + one NCCL gather + un-tile kernel
+    peer = args.gather == "peer"
     tg = mg.TileGather(w, h, rank, world, dev, rtp)
+    img = mg.PeerImage(w, h, rank, world, local, rtp)
     rgb8 = torch.zeros(w * h * 3, dtype=torch.uint8, device=dev) if rank == 0 else None
     rgb8_host = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory() if rank == 0 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
 
     def step(profile=False):
-        mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None,
-                        flags=rtp.RENDER_PROFILE if profile else 0)
+        flags = rtp.RENDER_PROFILE if profile else 0
+        if peer:
+            mg.render_frame_peer(scene, img, md, stream, flags=flags)
+        else:
+            mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None, flags=flags)
+
+    # both routes must deliver the same bytes
+    mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None)
+    mg.render_frame_peer(scene, img, md, stream)
+    torch.cuda.synchronize()
+    same = bool(torch.equal(img.rgb8_tensor(img.frame - 1).reshape(-1), rgb8)) if rank == 0 else True
+    if not same:
+        raise SystemExit("bench.py: the peer-store image differs from the NCCL-gathered image")
 
     def sync_all():
         if world > 1:
@@ -282,7 +313,7 @@ def run_ours(args, wl, rtp):
         k_any.append(fs["ms_anyhit"])
         k_shade.append(fs["ms_shade"])
     clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
-    launches_rank0 = (fs["kernel_launches"] + (1 if rank == 0 else 0)) * args.steps  # frame kernels + untile on rank 0
+    launches_rank0 = (fs["kernel_launches"] + (0 if peer else 1)) * args.steps  # frame kernels (+ un-tile on rank 0)
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
     e2e_ms = []
@@ -297,7 +328,8 @@ def run_ours(args, wl, rtp):
         else:
             step()
             if rank == 0:
-                rgb8_host.copy_(rgb8, non_blocking=True)
+                src = img.rgb8_tensor(img.frame - 1).reshape(-1) if peer else rgb8
+                rgb8_host.copy_(src, non_blocking=True)
         sync_all()
         if it > 0:
             t = torch.tensor([1e3 * (time.perf_counter() - t0)], device=dev)
@@ -332,13 +364,17 @@ def run_ours(args, wl, rtp):
                     dtype="f32", data="synthetic",
                     config=dict(workload=wl["desc"], rays_per_frame=rays_frame, triangles=n_tris, bvh_nodes=info["n_bvh_nodes"],
                                 parallelism=f"tile{world}" if world > 1 else "1gpu",
+                                gather=("resolve kernel stores tiles into GPU 0's image (CUDA IPC peer memory) + 4-byte all-reduce"
+                                        if peer else "NCCL gather of tile buffers + un-tile kernel") if world > 1 else
+                                       "resolve kernel writes the image (1 GPU)" if peer else "un-tile kernel (1 GPU)",
+                                peer_image_equals_nccl_gather=same,
                                 l2="256 MiB memset between timed steps (untimed) flushes the 126 MB L2",
                                 scene_build_s=round(t_build, 2)),
                     clocks=clocks,
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=cam_bytes, d2h_bytes_per_step=w * h * 3,
                              ms_per_step=float(np.mean(e2e_ms)),
                              what="rtp_set_lights + rtp_set_camera + rtp_render -> host uint8 image" if world == 1 else
-                                  "set lights/camera + tile render + NCCL gather + untile + D2H of the uint8 image on rank 0"),
+                                  "set lights/camera + tile render into GPU 0's image + D2H of the uint8 image on rank 0"),
                     gpu_launches=launches_rank0,
                     roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
                                   traffic=traffic, kernel=dom, kernel_ms=dom_ms, rays_per_launch_set=dom_rays,
@@ -349,6 +385,149 @@ def run_ours(args, wl, rtp):
                                              grays_per_s_kernel=dom_rays / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0)))
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(wl)
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+    img.close()
+    scene.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_c5(args, wl, rtp):
+    """C5: 64 ambient-occlusion rays per primary hit, traced as any-hit queries through
+    rtp_trace_rays_device; the hit points are split into one contiguous share per GPU (no data-path
+    collective), the per-pixel occlusion sums are gathered to rank 0."""
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the hot path is CUDA only (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    m, w, h, n_ao = wl["mesh"], wl["w"], wl["h"], wl["ao"]
+    scene = rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], device=local)
+    scene.set_lights(wl["lights"], None)
+    scene.set_camera(w, h, wl["view"])
+    info = scene.info()
+    stream = torch.cuda.current_stream().cuda_stream
+    # hit points + geometric normals of the primary frame (workload generation, untimed)
+    eye = np.asarray(wl["eye"], np.float32)
+    out = scene.render(w, h, max_depth=1, want=("hit",))
+    hit = out["hit"].ravel()
+    keep = np.nonzero(hit >= 0)[0]
+    share = np.array_split(keep, world)[rank]
+    f = np.asarray(m["faces"])[hit[share]]
+    shp = np.asarray(m["shape"], np.float32).reshape(3, 4)
+    V = (np.asarray(m["verts"], np.float32)[:, :3] @ shp[:, :3].T + shp[:, 3]).astype(np.float32)
+    P = torch.from_numpy((V[f[:, 0]] + V[f[:, 1]] + V[f[:, 2]]) / np.float32(3)).to(dev)  # centroid of the hit triangle
+    n = np.cross(V[f[:, 1]] - V[f[:, 0]], V[f[:, 2]] - V[f[:, 0]])
+    n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
+    N = torch.from_numpy(n.astype(np.float32)).to(dev)
+    N = torch.where(((torch.from_numpy(eye).to(dev)[None, :] - P) * N).sum(1, keepdim=True) < 0, -N, N)
+    g = torch.Generator(device=dev)
+    g.manual_seed(1234 + rank)
+    d = torch.randn((len(share), n_ao, 3), device=dev, generator=g)
+    d = d / d.norm(dim=2, keepdim=True)
+    d = torch.where((d * N[:, None, :]).sum(2, keepdim=True) < 0, -d, d)
+    o = (P + 0.003 * N)[:, None, :].expand(-1, n_ao, -1)
+    rays = torch.cat([o, d], 2).reshape(-1, 6).contiguous()
+    n_rays = rays.shape[0]
+    occ = torch.zeros(n_rays, dtype=torch.uint8, device=dev)
+    ao = torch.zeros(len(share), dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    cnt = torch.tensor([len(share)], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(sizes, cnt)
+    maxn = int(max(int(x.item()) for x in sizes)) if world > 1 else len(share)
+    pad = torch.zeros(maxn, dtype=torch.float32, device=dev)
+    gathered = [torch.zeros(maxn, dtype=torch.float32, device=dev) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def step():
+        scene.trace_rays_device(rays.data_ptr(), n_rays, rtp.RAYS_ANYHIT, d_occ=occ.data_ptr(), stream=stream)
+        torch.sum(occ.view(-1, n_ao), dim=1, dtype=torch.float32, out=ao)
+        if world > 1:
+            pad[:len(share)] = ao
+            dist.gather(pad, gathered, dst=0)
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+    total = torch.tensor([n_rays], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(total)
+    rays_step = int(total.item())
+    t_begin = time.perf_counter()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ms_steps = []
+    for _ in range(args.steps):
+        flush.zero_()
+        sync_all()
+        ev0.record()
+        step()
+        ev1.record()
+        sync_all()
+        t = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_steps.append(float(t.item()))
+    clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
+    # end to end: rays from pinned host memory, occlusion flags back to the host (a bounded slice: the full list is 3 GB)
+    n_e2e = min(n_rays, 8 << 20)
+    h_rays = rays[:n_e2e].cpu().pin_memory()
+    h_occ = torch.zeros(n_e2e, dtype=torch.uint8).pin_memory()
+    d_rays2 = torch.empty_like(rays[:n_e2e])
+    e2e_ms = []
+    for it in range(4):
+        sync_all()
+        t0 = time.perf_counter()
+        d_rays2.copy_(h_rays, non_blocking=True)
+        scene.trace_rays_device(d_rays2.data_ptr(), n_e2e, rtp.RAYS_ANYHIT, d_occ=occ.data_ptr(), stream=stream)
+        h_occ.copy_(occ[:n_e2e], non_blocking=True)
+        sync_all()
+        if it > 0:
+            e2e_ms.append(1e3 * (time.perf_counter() - t0))
+    if rank == 0:
+        total_ms = sum(ms_steps)
+        value = rays_step * args.steps / (total_ms / 1e3) / 1e6
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        n_tris = info["n_triangles"]
+        k_ms = total_ms / args.steps  # the any-hit trace kernel is >99% of the step
+        achieved = n_rays * b_alg(n_tris) / (k_ms / 1e3) / 1e9
+        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                    ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
+                    dtype="f32", data="synthetic",
+                    config=dict(workload=wl["desc"], rays_per_step=rays_step, triangles=n_tris, bvh_nodes=info["n_bvh_nodes"],
+                                parallelism=f"rays{world}" if world > 1 else "1gpu",
+                                l2="256 MiB memset between timed steps (untimed); the 3.2 GB ray list alone exceeds the L2"),
+                    clocks=clocks,
+                    e2e=dict(value=n_e2e * world * len(e2e_ms) / (sum(e2e_ms) / 1e3) / 1e6, unit=UNIT,
+                             h2d_bytes_per_step=n_e2e * 24, d2h_bytes_per_step=n_e2e, ms_per_step=float(np.mean(e2e_ms)),
+                             what=f"{n_e2e} rays per GPU from pinned host memory -> rtp_trace_rays_device(any-hit) -> occlusion bytes to the host"),
+                    gpu_launches=args.steps,
+                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=None,
+                                  kernel="k_trace<RaysAny>", kernel_ms=k_ms, rays_per_launch_set=float(n_rays),
+                                  alg_bytes_per_ray=b_alg(n_tris) + 24,
+                                  peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
+                                  note="kernel_ms = step time (the trace kernel plus the per-pixel sum / gather)"))
         print(json.dumps(line))
     scene.close()
     if world > 1:
@@ -361,14 +540,17 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3"])
+    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
     args = ap.parse_args()
     rtp = importlib.import_module("ray-tracing-project_b200")
     synth = importlib.import_module("ray-tracing-project_b200.synth")
     wl = build_workload(args.workload, synth)
     if args.impl == "reference":
         run_reference(args, wl, synth)
+    elif args.workload == "c5":
+        run_c5(args, wl, rtp)
     else:
         run_ours(args, wl, rtp)
 

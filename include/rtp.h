@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 1
+#define RTP_ABI_VERSION 2
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -141,6 +141,22 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
  * skip.  d_rgb: W*H*3 float, d_rgb8: W*H*3 uint8, d_hit: W*H int32. */
 int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void *d_all,
                       size_t rank_stride_bytes, void *d_rgb, void *d_rgb8, void *d_hit, void *stream);
+
+/* Fused variant of the two calls above: this rank's tiles are resolved straight into the finished
+ * row-major image - d_rgb8 (W*H*3 uint8, the values writePPMImage prints, ppmIO.hpp:150) and/or d_hit
+ * (W*H int32 primary face ids), either may be NULL - with 96-byte row segments per warp.  The
+ * pointers may address ANOTHER GPU's memory (rtp_shared_open below): every rank then stores its tiles
+ * into GPU 0's image over NVLink from inside the resolve kernel and no gather / un-tile pass is left;
+ * the caller only has to order GPU 0's readers after all ranks' streams (a barrier).  Replaces the
+ * join + image assembly of raytraceScene (flyscene.cpp:261-264,287-292).  Asynchronous on `stream`. */
+int rtp_render_image_device(rtp_scene *s, const rtp_render_opts *o, void *d_rgb8, void *d_hit, void *stream,
+                            rtp_stats *st);
+/* Device buffers shareable between the processes of one box (CUDA IPC): the owner allocates and
+ * exports a 64-byte handle, peers map it (peer access over NVLink is enabled on first use). */
+#define RTP_SHARED_HANDLE_BYTES 64
+int rtp_shared_alloc(int device, size_t bytes, void **d_ptr, void *handle /* RTP_SHARED_HANDLE_BYTES */);
+int rtp_shared_open(int device, const void *handle, void **d_ptr);
+int rtp_shared_free(int device, void *d_ptr, int opened /* 1: came from rtp_shared_open */);
 
 /* ---- single-ray API ---------------------------------------------------------------------- */
 typedef enum rtp_ray_mode {

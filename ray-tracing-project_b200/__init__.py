@@ -61,7 +61,8 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats", "rtp_tile_table"]
+           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
+           "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free"]
 
 _lib = None
 
@@ -100,6 +101,11 @@ def lib():
         L.rtp_scene_info.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
         L.rtp_frame_stats.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
         L.rtp_tile_table.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        L.rtp_render_image_device.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
+                                              C.POINTER(RtpStats)]
+        L.rtp_shared_alloc.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p), C.c_void_p]
+        L.rtp_shared_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.rtp_shared_free.argtypes = [C.c_int, C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -250,6 +256,16 @@ class Scene:
                                                     C.byref(st) if want_stats else None))
         return st.as_dict() if want_stats else None
 
+    def render_image_device(self, w, h, d_rgb8=None, d_hit=None, max_depth=2, background=BACKGROUND, rank=0, world=1,
+                            stream=None, want_stats=False, flags=0):
+        """rtp_render_image_device: this rank's tiles resolved straight into the finished image planes
+        (which may be peer memory on another GPU)."""
+        o = make_opts(w, h, max_depth, background, rank, world, flags)
+        st = RtpStats()
+        self._check(self._L.rtp_render_image_device(self._h, C.byref(o), d_rgb8, d_hit, stream,
+                                                    C.byref(st) if want_stats else None))
+        return st.as_dict() if want_stats else None
+
     def untile_device(self, w, h, world, d_all_ptr, rank_stride_bytes, d_rgb=None, d_rgb8=None, d_hit=None,
                       stream=None):
         self._check(self._L.rtp_untile_device(self._h, w, h, world, d_all_ptr, rank_stride_bytes, d_rgb, d_rgb8,
@@ -280,6 +296,31 @@ class Scene:
         self._check(self._L.rtp_trace_rays_device(self._h, d_rays_ptr, n, mode, d_face, d_t, d_occ, stream,
                                                   C.byref(st) if want_stats else None))
         return st.as_dict() if want_stats else None
+
+
+SHARED_HANDLE_BYTES = 64
+
+
+def _rc(rc, what):
+    if rc != 0:
+        raise RtpError(f"{what}: rtp error {rc}: {lib().rtp_last_error().decode(errors='replace')}")
+
+
+def shared_alloc(device, nbytes):
+    """(device pointer, 64-byte CUDA IPC handle) of a zero-filled buffer other processes can map."""
+    ptr, handle = C.c_void_p(), C.create_string_buffer(SHARED_HANDLE_BYTES)
+    _rc(lib().rtp_shared_alloc(device, nbytes, C.byref(ptr), handle), "rtp_shared_alloc")
+    return ptr.value, handle.raw
+
+
+def shared_open(device, handle):
+    ptr = C.c_void_p()
+    _rc(lib().rtp_shared_open(device, C.create_string_buffer(handle, SHARED_HANDLE_BYTES), C.byref(ptr)), "rtp_shared_open")
+    return ptr.value
+
+
+def shared_free(device, ptr, opened):
+    _rc(lib().rtp_shared_free(device, ptr, 1 if opened else 0), "rtp_shared_free")
 
 
 def tile_buffer_bytes(w, h, rank=0, world=1):

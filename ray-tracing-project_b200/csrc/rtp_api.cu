@@ -269,6 +269,8 @@ int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int wo
   const bool same = f.width == width && f.height == height && f.rank == rank && f.world == world &&
                     f.max_depth >= max_depth && f.n_px == n_paths && f.n_lights >= n_lights;
   if (same) return RTP_OK;
+  // the buffers below are about to be re-sized / re-filled: wait for the frame that may still use them
+  if (s->has_last) CK(cudaStreamSynchronize(s->last_stream));
   f.width = width; f.height = height; f.rank = rank; f.world = world; f.max_depth = max_depth; f.n_px = n_paths;
   f.n_lights = n_lights;
   f.tiles_x = (width + kTileDim - 1) / kTileDim;
@@ -305,6 +307,8 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
   p.max_depth = o.max_depth;
   p.bg[0] = o.background[0]; p.bg[1] = o.background[1]; p.bg[2] = o.background[2];
   p.fb = fb;
+  p.img_rgb8 = nullptr;
+  p.img_hit = nullptr;
   p.primface = f.primface.p; p.ksdeep = f.ksdeep.p; p.direct = f.direct.p;
   p.ray_o[0] = f.ray_o0.p; p.ray_o[1] = f.ray_o1.p; p.ray_d[0] = f.ray_d0.p; p.ray_d[1] = f.ray_d1.p;
   p.hit_t = f.hit_t.p; p.hit_slot = f.hit_slot.p;
@@ -445,6 +449,76 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   return RTP_OK;
 }
 
+int rtp_render_image_device(rtp_scene *s, const rtp_render_opts *o, void *d_rgb8, void *d_hit, void *stream,
+                            rtp_stats *st) {
+  int rc = check_render_args(s, o);
+  if (rc) return rc;
+  if (!d_rgb8 && !d_hit) return fail(RTP_ERR_INVALID, "rtp_render_image_device: no output plane");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = (cudaStream_t)stream;
+  const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
+  rc = ensure_frame(s, s->frame, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
+  if (rc) return rc;
+  Frame &f = s->frame;
+  FrameParams p;
+  fill_params(s, f, *o, nullptr, p);
+  p.img_rgb8 = (unsigned char *)d_rgb8;
+  p.img_hit = (int *)d_hit;
+  int launches = 0;
+  if (st) CK(cudaEventRecord(s->ev[0], cs));
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
+  if (rc) return rc;
+  if (st) {
+    CK(cudaEventRecord(s->ev[1], cs));
+    std::memset(st, 0, sizeof *st);
+    rc = read_stats(s, st, cs);
+    if (rc) return rc;
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
+    st->ms_total = st->ms_trace;
+    st->kernel_launches = launches;
+  }
+  return RTP_OK;
+}
+
+int rtp_shared_alloc(int device, size_t bytes, void **d_ptr, void *handle) {
+  if (!d_ptr || !handle || bytes == 0) return fail(RTP_ERR_INVALID, "rtp_shared_alloc: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == RTP_SHARED_HANDLE_BYTES, "CUDA IPC handle size");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(RTP_ERR_CUDA, "rtp_shared_alloc: cudaSetDevice failed");
+  *d_ptr = nullptr;
+  CK(cudaMalloc(d_ptr, bytes));  // a dedicated allocation: an IPC handle always names a whole cudaMalloc block
+  CK(cudaMemset(*d_ptr, 0, bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, *d_ptr);
+  if (e != cudaSuccess) {
+    cudaFree(*d_ptr);
+    *d_ptr = nullptr;
+    return fail(RTP_ERR_CUDA, std::string("cudaIpcGetMemHandle: ") + cudaGetErrorString(e));
+  }
+  std::memcpy(handle, &h, sizeof h);
+  return RTP_OK;
+}
+
+int rtp_shared_open(int device, const void *handle, void **d_ptr) {
+  if (!d_ptr || !handle) return fail(RTP_ERR_INVALID, "rtp_shared_open: bad argument");
+  DeviceGuard g(device);
+  if (!g.ok) return fail(RTP_ERR_CUDA, "rtp_shared_open: cudaSetDevice failed");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, sizeof h);
+  *d_ptr = nullptr;
+  CK(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return RTP_OK;
+}
+
+int rtp_shared_free(int device, void *d_ptr, int opened) {
+  if (!d_ptr) return RTP_OK;
+  DeviceGuard g(device);
+  if (!g.ok) return fail(RTP_ERR_CUDA, "rtp_shared_free: cudaSetDevice failed");
+  if (opened) CK(cudaIpcCloseMemHandle(d_ptr));
+  else CK(cudaFree(d_ptr));
+  return RTP_OK;
+}
+
 int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void *d_all, size_t rank_stride_bytes,
                       void *d_rgb, void *d_rgb8, void *d_hit, void *stream) {
   if (!s || !d_all || width <= 0 || height <= 0 || world < 1) return fail(RTP_ERR_INVALID, "rtp_untile_device: bad argument");
@@ -474,19 +548,25 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   if (rgb) CK(f.out_rgb.ensure(npix * 3));
   if (rgb8) CK(f.out_rgb8.ensure(npix * 3));
   if (hit) CK(f.out_hit.ensure(npix));
+  // no float plane wanted: the resolve kernel writes the finished rgb8 / hit planes itself (no un-tile pass)
+  const bool fused = !rgb && (rgb8 || hit);
   FrameParams p;
-  fill_params(s, f, *o, f.fb.p, p);
-  int launches = 0;
-  CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
-  if (rc) return rc;
-  CK(cudaEventRecord(s->ev[1], cs));
+  fill_params(s, f, *o, fused ? nullptr : f.fb.p, p);
   if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
     if (rgb) CK(cudaMemcpyAsync(f.out_rgb.p, rgb, npix * 3 * sizeof(float), cudaMemcpyHostToDevice, cs));
     if (rgb8) CK(cudaMemcpyAsync(f.out_rgb8.p, rgb8, npix * 3, cudaMemcpyHostToDevice, cs));
     if (hit) CK(cudaMemcpyAsync(f.out_hit.p, hit, npix * sizeof(int), cudaMemcpyHostToDevice, cs));
   }
-  if (rgb || rgb8 || hit) {
+  if (fused) {
+    p.img_rgb8 = rgb8 ? f.out_rgb8.p : nullptr;
+    p.img_hit = hit ? f.out_hit.p : nullptr;
+  }
+  int launches = 0;
+  CK(cudaEventRecord(s->ev[0], cs));
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
+  if (rc) return rc;
+  CK(cudaEventRecord(s->ev[1], cs));
+  if (!fused && (rgb || rgb8 || hit)) {
     launch_untile(f.fb.p, 0, f.local_of_tile.p, o->width, o->height, o->world, o->world > 1 ? o->rank : 0,
                   rgb ? f.out_rgb.p : nullptr, rgb8 ? f.out_rgb8.p : nullptr, hit ? f.out_hit.p : nullptr, cs);
     ++launches;

@@ -480,30 +480,60 @@ __global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int de
   }
 }
 
-__global__ void __launch_bounds__(256) k_resolve(const FrameParams p) {
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= p.n_px) return;
+// the fold of traceRay's return values (flyscene.cpp:366-370 with the member ks of the deepest hit)
+__device__ __forceinline__ float4 resolve_pixel(const FrameParams &p, int q) {
   const float4 kd = p.ksdeep[q];
   const int k = f2i(kd.w);
   const int face = p.primface[q];
-  float4 out;
-  if (face == -2) {
-    out = make_float4(0.f, 0.f, 0.f, i2f(-1));
-  } else if (k == 0) {
-    out = make_float4(p.bg[0], p.bg[1], p.bg[2], i2f(-1));  // flyscene.cpp:327-330
-  } else {
-    // deepest level: clamp(direct + 0 * ks) (the recursion below it returned (0,0,0))
-    float4 dc = p.direct[(size_t)(k - 1) * p.n_px + q];
-    v3 c = mk3(clamp01(fadd(dc.x, fmul(0.f, kd.x))), clamp01(fadd(dc.y, fmul(0.f, kd.y))),
-               clamp01(fadd(dc.z, fmul(0.f, kd.z))));
-    for (int d = k - 2; d >= 0; --d) {  // flyscene.cpp:366-370 with the member ks of the deepest hit
-      dc = p.direct[(size_t)d * p.n_px + q];
-      c = mk3(clamp01(fadd(dc.x, fmul(c.x, kd.x))), clamp01(fadd(dc.y, fmul(c.y, kd.y))),
-              clamp01(fadd(dc.z, fmul(c.z, kd.z))));
-    }
-    out = make_float4(c.x, c.y, c.z, i2f(face));
+  if (face == -2) return make_float4(0.f, 0.f, 0.f, i2f(-2));  // pixel outside the image
+  if (k == 0) return make_float4(p.bg[0], p.bg[1], p.bg[2], i2f(-1));  // flyscene.cpp:327-330
+  // deepest level: clamp(direct + 0 * ks) (the recursion below it returned (0,0,0))
+  float4 dc = p.direct[(size_t)(k - 1) * p.n_px + q];
+  v3 c = mk3(clamp01(fadd(dc.x, fmul(0.f, kd.x))), clamp01(fadd(dc.y, fmul(0.f, kd.y))),
+             clamp01(fadd(dc.z, fmul(0.f, kd.z))));
+  for (int d = k - 2; d >= 0; --d) {
+    dc = p.direct[(size_t)d * p.n_px + q];
+    c = mk3(clamp01(fadd(dc.x, fmul(c.x, kd.x))), clamp01(fadd(dc.y, fmul(c.y, kd.y))),
+            clamp01(fadd(dc.z, fmul(c.z, kd.z))));
   }
+  return make_float4(c.x, c.y, c.z, i2f(face));
+}
+
+// ppmIO.hpp:150: min(255, (int)(255*c)); NaN -> 0 (undefined in the reference)
+__device__ __forceinline__ unsigned char quantise(float c) {
+  const float s = fmul(255.f, c);
+  const int qv = (s != s) ? 0 : __float2int_rz(s);
+  return (unsigned char)min(255, max(qv, 0));
+}
+
+__global__ void __launch_bounds__(256) k_resolve(const FrameParams p) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= p.n_px) return;
+  float4 out = resolve_pixel(p, q);
+  if (f2i(out.w) == -2) out.w = i2f(-1);
   p.fb[q] = out;
+}
+
+// Resolve fused with the image assembly: thread r of a tile handles pixel (r & 31, r >> 5) of that
+// tile, so a warp writes 32 consecutive pixels of one image row (96 contiguous bytes) - the image may
+// be peer memory on GPU 0, reached over NVLink, and then this kernel IS the framebuffer gather.
+__global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= p.n_px) return;
+  const int local = r >> 10, x = r & 31, y = (r >> 5) & 31;
+  const int tile = __ldg(p.tile_ids + local);
+  const int i = (tile % p.tiles_x) * kTileDim + x, j = (tile / p.tiles_x) * kTileDim + y;
+  if (i >= p.width || j >= p.height) return;
+  const int q = (local << 10) + ((((y >> 2) * 4 + (x >> 3)) << 5) + ((y & 3) << 3) + (x & 7));
+  const float4 out = resolve_pixel(p, q);
+  const size_t idx = (size_t)j * p.width + i;
+  if (p.fb) p.fb[q] = out;
+  if (p.img_rgb8) {
+    p.img_rgb8[3 * idx] = quantise(out.x);
+    p.img_rgb8[3 * idx + 1] = quantise(out.y);
+    p.img_rgb8[3 * idx + 2] = quantise(out.z);
+  }
+  if (p.img_hit) p.img_hit[idx] = f2i(out.w);
 }
 
 __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile,
@@ -519,13 +549,10 @@ __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_s
   const int pix = (((y >> 2) * 4 + (x >> 3)) << 5) + ((y & 3) << 3) + (x & 7);
   const float4 v = all[(size_t)(only_rank >= 0 ? 0 : owner) * rank_stride_f4 + (size_t)local * kTilePixels + pix];
   if (rgb) { rgb[3 * idx] = v.x; rgb[3 * idx + 1] = v.y; rgb[3 * idx + 2] = v.z; }
-  if (rgb8) {  // ppmIO.hpp:150: min(255, (int)(255*c)); NaN -> 0 (undefined in the reference)
-    float c[3] = {v.x, v.y, v.z};
-    for (int k = 0; k < 3; ++k) {
-      float s = fmul(255.f, c[k]);
-      int qv = (s != s) ? 0 : __float2int_rz(s);
-      rgb8[3 * idx + k] = (unsigned char)min(255, max(qv, 0));
-    }
+  if (rgb8) {
+    rgb8[3 * idx] = quantise(v.x);
+    rgb8[3 * idx + 1] = quantise(v.y);
+    rgb8[3 * idx + 2] = quantise(v.z);
   }
   if (hit) hit[idx] = f2i(v.w);
 }
@@ -620,7 +647,10 @@ void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
   k_accum<<<(p.n_px + 255) / 256, 256, 0, st>>>(p, depth);
 }
 
-void launch_resolve(const FrameParams &p, cudaStream_t st) { k_resolve<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
+void launch_resolve(const FrameParams &p, cudaStream_t st) {
+  if (p.img_rgb8 || p.img_hit) k_resolve_image<<<(p.n_px + 255) / 256, 256, 0, st>>>(p);
+  else k_resolve<<<(p.n_px + 255) / 256, 256, 0, st>>>(p);
+}
 
 void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile, int width, int height,
                    int world, int only_rank, float *rgb, unsigned char *rgb8, int *hit, cudaStream_t st) {

@@ -27,7 +27,10 @@ struct FrameParams {
   int n_user_rays;
   int max_depth;
   float bg[3];
-  float4 *fb;        // out, tile-major: r, g, b, bit-cast primary face id
+  float4 *fb;        // out, tile-major: r, g, b, bit-cast primary face id (may be null when img_* is set)
+  unsigned char *img_rgb8;  // out, optional: the finished image, row-major W x H x 3, quantised like the PPM writer;
+  int *img_hit;             //   and the primary face ids, W x H.  Either may live on ANOTHER GPU (peer memory
+                            //   mapped through CUDA IPC): every rank stores its own tiles straight into GPU 0's image
   int *primface;     // [n_px] primary face id (-1 background, -2 pixel outside the image)
   float4 *ksdeep;    // [n_px] ks of the deepest hit, .w = hit-chain length bits
   float4 *direct;    // [max_depth][n_px] clamped direct colour per depth

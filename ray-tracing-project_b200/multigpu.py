@@ -3,8 +3,17 @@ split into interleaved 32x32 screen tiles (owner = (tx + ty) % world), ONE gathe
 tile-major buffers to rank 0 per frame (NCCL over NVLink on GPUs; the same code runs over gloo on
 CPU tensors in the tests), then the library's un-tile kernel on rank 0.
 
-This is plumbing only: buffers, the collective, call order.  The pixels come from
-rtp_render_tiles_device / rtp_untile_device (include/rtp.h); nothing is computed here.
+Two ways to bring the tiles to GPU 0:
+  * TileGather + render_frame: per-rank tile-major buffers, ONE NCCL gather per frame, un-tile kernel on
+    rank 0 (also what the gloo CPU tests drive);
+  * PeerImage + render_frame_peer: rank 0's image is mapped into every process through CUDA IPC and
+    each rank's resolve kernel stores its finished pixels straight into it over NVLink
+    (rtp_render_image_device) - the gather is fused into the last kernel of the frame; what is left
+    of the collective is a barrier.  The image is double-buffered so that rank 0 may still read
+    frame f while the others already write frame f + 1.
+
+This is plumbing only: buffers, the collective, call order.  The pixels come from the library
+(include/rtp.h); nothing is computed here.
 Replaces the row-band std::thread fan-out + join of the reference (src/flyscene.cpp:266-289).
 """
 import importlib
@@ -41,3 +50,60 @@ def render_frame(scene, tg, max_depth, stream, d_rgb8=None, d_rgb=None, d_hit=No
     if tg.rank == 0:
         scene.untile_device(tg.w, tg.h, tg.world, src.data_ptr(), tg.stride_bytes, d_rgb=d_rgb, d_rgb8=d_rgb8, d_hit=d_hit,
                             stream=stream)
+
+
+class PeerImage:
+    """GPU 0's finished image (W x H x 3 uint8, and optionally W x H int32 face ids), double-buffered,
+    mapped into every rank's address space through CUDA IPC (NVLink peer access)."""
+
+    def __init__(self, w, h, rank, world, device_index, rtp=None, with_hit=False):
+        self.rtp = rtp or importlib.import_module("ray-tracing-project_b200")
+        self.w, self.h, self.rank, self.world, self.dev, self.with_hit = w, h, rank, world, device_index, with_hit
+        self.rgb_bytes, self.hit_bytes = w * h * 3, (w * h * 4 if with_hit else 0)
+        self.stride = (self.rgb_bytes + self.hit_bytes + 255) // 256 * 256
+        handle = torch.zeros(self.rtp.SHARED_HANDLE_BYTES, dtype=torch.uint8, device=torch.device("cuda", device_index))
+        self.opened = False
+        if rank == 0:
+            self.base, raw = self.rtp.shared_alloc(device_index, 2 * self.stride)
+            handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
+        if world > 1:
+            dist.broadcast(handle, src=0)
+        if rank != 0:
+            self.base = self.rtp.shared_open(device_index, bytes(handle.cpu().numpy().tobytes()))
+            self.opened = True
+        self.frame = 0
+        self.token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
+
+    def planes(self, frame=None):
+        """(rgb8 pointer, hit pointer or None) of the buffer frame `frame` is written to."""
+        f = self.frame if frame is None else frame
+        p = self.base + (f & 1) * self.stride
+        return p, (p + self.rgb_bytes if self.with_hit else None)
+
+    def rgb8_tensor(self, frame):
+        """The rgb8 plane of `frame` as a torch tensor over the shared memory (no copy)."""
+        class _Span:
+            pass
+        sp = _Span()
+        sp.__cuda_array_interface__ = dict(shape=(self.h, self.w, 3), typestr="|u1", data=(self.planes(frame)[0], False), version=2)
+        return torch.as_tensor(sp, device=torch.device("cuda", self.dev))
+
+    def close(self):
+        if getattr(self, "base", None):
+            self.rtp.shared_free(self.dev, self.base, self.opened)
+            self.base = None
+
+
+def render_frame_peer(scene, img, max_depth, stream, flags=0):
+    """One frame: every rank renders its tiles and resolves them straight into rank 0's image (peer
+    stores over NVLink); a 4-byte all-reduce orders rank 0's readers after everybody's stores.  Returns the
+    (rgb8, hit) device pointers of the finished frame (meaningful on rank 0)."""
+    d_rgb8, d_hit = img.planes()
+    scene.render_image_device(img.w, img.h, d_rgb8=d_rgb8, d_hit=d_hit, max_depth=max_depth, rank=img.rank,
+                              world=img.world, stream=stream, flags=flags)
+    if img.world > 1:
+        # a 4-byte all-reduce as a stream-ordered barrier: it starts after this rank's stores (same stream)
+        # and completes on rank 0 only when every rank has started it; the host is not blocked
+        dist.all_reduce(img.token)
+    img.frame += 1
+    return d_rgb8, d_hit

@@ -107,6 +107,32 @@ def test_tile_sharding_is_bitwise_equal_to_one_gpu(rtp):
     s.close()
 
 
+def test_fused_resolve_writes_the_same_image_as_gather_and_untile(rtp):
+    """rtp_render_image_device: every (virtual) rank resolves its tiles straight into one shared image -
+    the multi-GPU drivers point it at GPU 0's memory - and the result must equal the un-tile path bit
+    for bit: quantised rgb8 (ppmIO.hpp:150) and primary face ids, including ragged edge tiles."""
+    import torch
+    c = load_case("dodge_c2")
+    m = load_golden_mesh("dodgeColorTest")
+    w, h = 203, 149  # not multiples of the 32-pixel tile
+    s = make_scene(rtp, m)
+    s.set_lights(c["point_lights"], None)
+    s.set_camera(w, h, c["view"])
+    full = s.render(w, h, max_depth=3, want=("rgb", "rgb8", "hit"))           # un-tile path (float plane requested)
+    fused1 = s.render(w, h, max_depth=3, want=("rgb8", "hit"))                # fused path inside rtp_render
+    assert np.array_equal(fused1["rgb8"], full["rgb8"]) and np.array_equal(fused1["hit"], full["hit"])
+    st = torch.cuda.current_stream().cuda_stream
+    for world in (1, 2, 5, 8):
+        img = torch.full((h, w, 3), 77, dtype=torch.uint8, device="cuda")
+        hit = torch.full((h, w), -9, dtype=torch.int32, device="cuda")
+        for r in range(world):
+            s.render_image_device(w, h, d_rgb8=img.data_ptr(), d_hit=hit.data_ptr(), max_depth=3, rank=r, world=world, stream=st)
+        torch.cuda.synchronize()
+        assert np.array_equal(img.cpu().numpy(), full["rgb8"]), f"rgb8 differs at world {world}"
+        assert np.array_equal(hit.cpu().numpy(), full["hit"]), f"face ids differ at world {world}"
+    s.close()
+
+
 def test_reference_box_filter_is_reproduced(rtp, po):
     """Faces whose BoundingBox fails the reference's own slab test are invisible (Q11/Q13): with
     artificially shrunken boxes this hits the deferred visibility check and the exact re-run."""
