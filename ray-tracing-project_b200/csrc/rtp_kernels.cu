@@ -275,25 +275,32 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
   int q = 0, age = 0;  // age: steps since this warp last took rays (warp-uniform)
   bool have = false, exhausted = false;
   for (;;) {
-    unsigned act = __ballot_sync(kFull, have);
-    if (!exhausted && __popc(act) < kRefillBelow) {
-      // refill every idle lane with the next rays of the global list
-      const unsigned need = ~act;
-      const int n_need = __popc(need);
-      const int leader = __ffs(need) - 1;
-      int base = 0;
-      if (lane == leader) base = atomicAdd(job.cursor, n_need);
-      base = __shfl_sync(kFull, base, leader);
-      exhausted = base + n_need >= count;
-#ifdef RTP_TRACE_TIMING
-      if (base < count) { tm_fetch = gtime(); ++tm_nb; }
-#endif
-      if (!have) {
-        q = base + __popc(need & lt);
-        if (q < count) have = job.init(q, t, stack);
-      }
+    // lanes whose traversal is still going (a finished one keeps its result in t until it is retired)
+    unsigned act = __ballot_sync(kFull, have && t.node != kSentinel);
+    if (__popc(act) < kRefillBelow) {
+      // retire: every lane whose traversal has ended writes its result NOW, together - the deferred
+      // BoundingBox check of a closest hit is ~60 instructions and used to run one lane at a time
+      if (have && t.node == kSentinel) have = !job.finish(q, t, stack);  // false: careful re-run, node = root again
       act = __ballot_sync(kFull, have);
-      age = 0;
+      if (!exhausted && __popc(act) < kRefillBelow) {
+        // refill every idle lane with the next rays of the global list
+        const unsigned need = ~act;
+        const int n_need = __popc(need);
+        const int leader = __ffs(need) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(job.cursor, n_need);
+        base = __shfl_sync(kFull, base, leader);
+        exhausted = base + n_need >= count;
+#ifdef RTP_TRACE_TIMING
+        if (base < count) { tm_fetch = gtime(); ++tm_nb; }
+#endif
+        if (!have) {
+          q = base + __popc(need & lt);
+          if (q < count) have = job.init(q, t, stack);
+        }
+        act = __ballot_sync(kFull, have);
+        age = 0;
+      }
     }
     if (act == 0) {
       if (exhausted) break;
@@ -301,7 +308,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
     }
     if (++age > pl.budget && __popc(act) <= pl.lanes) {
       // only stragglers are left in this warp: park them for k_coop
-      if (have) {
+      if (have && t.node != kSentinel) {
         const int at = atomicAdd(pl.ctr, 1);
         if (at < pl.cap) {
           int *e = pl.slots + (size_t)at * kParkInts;
@@ -322,7 +329,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
       age = 0;
       continue;
     }
-    if (have && trav_step<Job::kAny>(job.S, t, stack, job.box_origin(q, t))) have = !job.finish(q, t, stack);
+    if (have && t.node != kSentinel) trav_step<Job::kAny>(job.S, t, stack, job.box_origin(q, t));
   }
 #ifdef RTP_TRACE_TIMING
   if (lane == 0) {
