@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 2
+#define RTP_ABI_VERSION 3
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -58,7 +58,12 @@ typedef struct rtp_mesh {
   const int32_t *box_faces;   /* F face ids in box order */
   int32_t min_faces;          /* Flyscene::MIN_FACES (300) when 0 */
   int32_t max_boxes;          /* Flyscene::MAX_BOXES (INT_MAX) when 0 */
+  int32_t build;              /* RTP_BUILD_*: where the traversal hierarchy over the faces is built */
+  int32_t reserved;
 } rtp_mesh;
+#define RTP_BUILD_HOST_SAH 0 /* binned SAH on the host threads: best trees (default)                          */
+#define RTP_BUILD_GPU_LBVH 1 /* Morton sort + radix tree on the device: ~50x faster to build, slower to trace; */
+                             /* the image is the same either way (the hierarchy only culls)                    */
 
 /* Tucano::Camera state read by screenToWorld / getCenter (camera.hpp:115-118,155-173). */
 typedef struct rtp_camera {

@@ -32,7 +32,7 @@ class RtpMesh(C.Structure):
                 ("verts", _f32p), ("normals", _f32p), ("faces", _i32p), ("face_mat", _i32p),
                 ("face_normal", _f32p), ("materials", _f32p), ("shape", C.c_float * 12),
                 ("boxes", _f32p), ("box_off", _i32p), ("box_faces", _i32p),
-                ("min_faces", C.c_int32), ("max_boxes", C.c_int32)]
+                ("min_faces", C.c_int32), ("max_boxes", C.c_int32), ("build", C.c_int32), ("reserved", C.c_int32)]
 
 
 class RtpCamera(C.Structure):
@@ -120,8 +120,11 @@ def _i32(a, shape=None):
     return a.reshape(shape) if shape else a
 
 
+BUILD_HOST_SAH, BUILD_GPU_LBVH = 0, 1
+
+
 def make_mesh_struct(verts, normals, faces, face_mat, materials, shape, face_normal=None, boxes=None,
-                     box_off=None, box_faces=None, min_faces=0, max_boxes=0):
+                     box_off=None, box_faces=None, min_faces=0, max_boxes=0, build=0):
     """Builds an rtp_mesh over numpy arrays; returns (struct, keepalive list)."""
     verts, normals = _f32(verts, (-1, 4)), _f32(normals, (-1, 3))
     faces, face_mat = _i32(faces, (-1, 3)), _i32(face_mat, (-1,))
@@ -143,7 +146,7 @@ def make_mesh_struct(verts, normals, faces, face_mat, materials, shape, face_nor
         m.n_boxes = len(boxes)
         m.boxes, m.box_off, m.box_faces = (boxes.ctypes.data_as(_f32p), box_off.ctypes.data_as(_i32p),
                                            box_faces.ctypes.data_as(_i32p))
-    m.min_faces, m.max_boxes = min_faces, max_boxes
+    m.min_faces, m.max_boxes, m.build = min_faces, max_boxes, build
     return m, keep
 
 
@@ -180,11 +183,11 @@ class Scene:
     """A scene on one CUDA device (rtp_scene handle)."""
 
     def __init__(self, verts, normals, faces, face_mat, materials, shape, face_normal=None, boxes=None,
-                 box_off=None, box_faces=None, device=-1, min_faces=0, max_boxes=0):
+                 box_off=None, box_faces=None, device=-1, min_faces=0, max_boxes=0, build=0):
         self._h = C.c_void_p()
         self._L = lib()
         m, keep = make_mesh_struct(verts, normals, faces, face_mat, materials, shape, face_normal, boxes,
-                                   box_off, box_faces, min_faces, max_boxes)
+                                   box_off, box_faces, min_faces, max_boxes, build)
         self._check(self._L.rtp_scene_create(C.byref(m), device, C.byref(self._h)))
         self.n_faces = m.n_faces
         del keep

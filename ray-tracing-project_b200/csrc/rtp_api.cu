@@ -3,12 +3,14 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
 #include <vector>
 
 #include "../../include/rtp.h"
+#include "bvh_build_gpu.h"
 #include "rtp_kernels.h"
 #include "scene_host.h"
 
@@ -134,9 +136,13 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   rtp_scene *s = new (std::nothrow) rtp_scene();
   if (!s) return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory");
   s->device = device;
+  // where the traversal hierarchy is built: rtp_mesh.build, overridden by RTP_BVH_BUILD=gpu|host
+  bool gpu_build = mesh->build == RTP_BUILD_GPU_LBVH;
+  if (const char *be = std::getenv("RTP_BVH_BUILD")) gpu_build = std::string(be) == "gpu";
+  if (mesh->n_faces < 64) gpu_build = false;  // tiny scenes: nothing to gain
   std::string msg;
   try {
-    msg = flatten_scene(*mesh, s->host);
+    msg = flatten_scene(*mesh, s->host, 0, !gpu_build);
   } catch (const std::bad_alloc &) {
     delete s;
     return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory while flattening");
@@ -156,12 +162,36 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   for (auto &ev : s->ev)
     if ((e = cudaEventCreate(&ev)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
   HostScene &h = s->host;
-  if ((e = s->nodes.upload(h.nodes, s->stream)) != cudaSuccess) return cleanup(e, "upload nodes");
-  if ((e = s->tris.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
-  if ((e = s->vnorm.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
+  if (gpu_build) {
+    // rank-ordered triangles go up once; the device sorts them, builds the hierarchy and permutes
+    DevBuf<float4> tris_in, vnorm_in;
+    DevBuf<int> face_in;
+    const size_t n = (size_t)h.n_tris;
+    if ((e = tris_in.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
+    if ((e = vnorm_in.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
+    if ((e = face_in.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face ids");
+    if ((e = s->tris.ensure(4 * n)) != cudaSuccess) return cleanup(e, "alloc tris");
+    if ((e = s->vnorm.ensure(3 * n)) != cudaSuccess) return cleanup(e, "alloc vnorm");
+    if ((e = s->face_of.ensure(n)) != cudaSuccess) return cleanup(e, "alloc face_of");
+    if ((e = s->nodes.ensure(4 * n)) != cudaSuccess) return cleanup(e, "alloc nodes");
+    int n_nodes = 0, height = 0;
+    e = build_lbvh_device(tris_in.p, vnorm_in.p, face_in.p, h.n_tris, h.pad, h.scene_lo, h.scene_hi, 4, s->tris.p, s->vnorm.p,
+                          s->face_of.p, s->nodes.p, &n_nodes, &height, s->stream);
+    if (e != cudaSuccess) return cleanup(e, "build_lbvh_device");
+    if (height >= kStackSize - 2) {
+      delete s;
+      return fail(RTP_ERR_INVALID, "device-built BVH is deeper than the traversal stack; use RTP_BUILD_HOST_SAH");
+    }
+    h.n_nodes = n_nodes;
+    h.bvh_depth = height;
+  } else {
+    if ((e = s->nodes.upload(h.nodes, s->stream)) != cudaSuccess) return cleanup(e, "upload nodes");
+    if ((e = s->tris.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
+    if ((e = s->vnorm.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
+    if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
+  }
   if ((e = s->boxes.upload(h.boxes, s->stream)) != cudaSuccess) return cleanup(e, "upload boxes");
   if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
-  if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
   if ((e = s->counters.ensure(kCtrInts)) != cudaSuccess) return cleanup(e, "alloc counters");
   if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");

@@ -15,7 +15,7 @@ namespace rtp {
 static inline float4 f4(v3 a, float w) { return make_float4(a.x, a.y, a.z, w); }
 static inline v3 ld3(const float *p) { return mk3(p[0], p[1], p[2]); }
 
-std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads) {
+std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool with_bvh) {
   if (m.n_verts <= 0 || m.n_faces <= 0 || !m.verts || !m.normals || !m.faces || !m.face_mat)
     return "rtp_mesh: verts/normals/faces/face_mat must be non-empty";
   if (m.n_mats > 0 && !m.materials) return "rtp_mesh: n_mats > 0 but materials is NULL";
@@ -77,6 +77,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads) {
   std::vector<float4> T((size_t)n * 4), N((size_t)n * 3);
   std::vector<Aabb> bounds((size_t)n);
   float maxabs = 1.f;
+  for (int a = 0; a < 3; ++a) { out.scene_lo[a] = FLT_MAX; out.scene_hi[a] = -FLT_MAX; }
   out.n_flagged = out.n_degenerate = 0;
   std::vector<int32_t> box_of_rank((size_t)n);
   for (int b = 0; b < out.n_boxes; ++b)
@@ -126,6 +127,11 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads) {
       bb.hi[a] = std::max(c0, std::max(c1, c2));
       if (finite) maxabs = std::max(maxabs, std::max(std::fabs(bb.lo[a]), std::fabs(bb.hi[a])));
     }
+    if (finite)
+      for (int a = 0; a < 3; ++a) {
+        out.scene_lo[a] = std::min(out.scene_lo[a], bb.lo[a]);
+        out.scene_hi[a] = std::max(out.scene_hi[a], bb.hi[a]);
+      }
     if (!finite)
       for (int a = 0; a < 3; ++a) { bb.lo[a] = -FLT_MAX; bb.hi[a] = FLT_MAX; }
   }
@@ -134,6 +140,15 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads) {
   float pad_rel = 3e-5f;
   if (const char *e = std::getenv("RTP_BVH_PAD")) pad_rel = (float)std::atof(e);
   out.pad = pad_rel * maxabs;
+  if (!with_bvh) {  // rank order; the device builder sorts, fits and permutes (bvh_build_gpu.cu)
+    out.n_nodes = 0;
+    out.bvh_depth = 0;
+    out.nodes.clear();
+    out.tris.swap(T);
+    out.vnorm.swap(N);
+    out.face_of = out.box_faces;
+    return "";
+  }
   for (Aabb &bb : bounds)
     for (int a = 0; a < 3; ++a)
       if (bb.hi[a] < FLT_MAX) { bb.lo[a] -= out.pad; bb.hi[a] += out.pad; }

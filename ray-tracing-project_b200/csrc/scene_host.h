@@ -26,10 +26,12 @@ struct HostScene {
   int n_flagged = 0;     // triangles that need the zero-normal check
   int n_degenerate = 0;  // triangles whose face normal is not finite/unit (edge-case list)
   float pad = 0.f;       // AABB padding used
+  float scene_lo[3] = {0, 0, 0}, scene_hi[3] = {0, 0, 0};  // bounds of the finite (unpadded) triangles
 };
 
-// Returns "" on success, else an error message.
-std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads = 0);
+// Returns "" on success, else an error message.  with_bvh = false: no hierarchy is built; tris / vnorm /
+// face_of stay in reference rank order and nodes stays empty (the device builder takes over).
+std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads = 0, bool with_bvh = true);
 
 // Camera::getCenter, getViewMatrix().inverse(), perspective scale (camera.hpp:115-118,155-173,263-266)
 void derive_camera(const rtp_camera &c, DeviceCamera &out);

@@ -23,12 +23,12 @@ def test_header_symbols_are_exported(rtp):
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/rtp.h but not exported"
     assert sorted(rtp.EXPORTS) == names
-    assert L.rtp_abi_version() == 2
+    assert L.rtp_abi_version() == 3
 
 
 def test_struct_sizes_match_header(rtp):
     # plain C structs: sizes follow from the header's field lists (LP64)
-    assert C.sizeof(rtp.RtpMesh) == 16 + 6 * 8 + 48 + 3 * 8 + 8
+    assert C.sizeof(rtp.RtpMesh) == 16 + 6 * 8 + 48 + 3 * 8 + 16
     assert C.sizeof(rtp.RtpCamera) == 48 + 16 + 8
     assert C.sizeof(rtp.RtpRenderOpts) == 12 + 12 + 12
     assert C.sizeof(rtp.RtpStats) == 32 + 8 + 12 + 12

@@ -14,9 +14,9 @@ pytestmark = pytest.mark.gpu
 TOL = 1.0 / 255.0
 
 
-def make_scene(rtp, m, with_boxes=False):
+def make_scene(rtp, m, with_boxes=False, build=0):
     kw = dict(boxes=m.boxes, box_off=m.box_off, box_faces=m.box_faces) if with_boxes else {}
-    return rtp.Scene(m.verts, m.normals, m.faces, m.face_mat, m.materials, m.shape, **kw)
+    return rtp.Scene(m.verts, m.normals, m.faces, m.face_mat, m.materials, m.shape, build=build, **kw)
 
 
 def check_image(got_rgb, got_hit, ref_rgb, ref_hit, exact_fraction=0.5):
@@ -131,6 +131,27 @@ def test_fused_resolve_writes_the_same_image_as_gather_and_untile(rtp):
         assert np.array_equal(img.cpu().numpy(), full["rgb8"]), f"rgb8 differs at world {world}"
         assert np.array_equal(hit.cpu().numpy(), full["hit"]), f"face ids differ at world {world}"
     s.close()
+
+
+@pytest.mark.parametrize("name", ["dodge_c2", "dodge_c1", "testding_2l", "glas_nan", "quirks"])
+def test_gpu_built_bvh_gives_the_same_image(rtp, name):
+    """RTP_BUILD_GPU_LBVH (csrc/bvh_build_gpu.cu: Morton sort, radix tree, bottom-up fit on the device) only
+    changes how candidates are culled: hits, t order and colours must equal the host-SAH scene bit for bit."""
+    c = load_case(name)
+    m = load_golden_mesh(c["model"])
+    w, h = int(c["w"]), int(c["h"])
+    out = []
+    for build in (rtp.BUILD_HOST_SAH, rtp.BUILD_GPU_LBVH):
+        s = make_scene(rtp, m, build=build)
+        s.set_lights(c["point_lights"], c["dir_lights"])
+        s.set_camera(w, h, c["view"])
+        out.append(s.render(w, h, max_depth=int(c["max_depth"])))
+        info = s.info()
+        assert info["n_triangles"] == len(m.faces) and info["n_bvh_nodes"] > 0
+        s.close()
+    assert np.array_equal(out[0]["hit"], out[1]["hit"])
+    assert bits_equal(out[0]["rgb"], out[1]["rgb"]).all()
+    check_image(out[1]["rgb"].reshape(-1, 3), out[1]["hit"].ravel(), c["rgb"], c["hit"])
 
 
 def test_reference_box_filter_is_reproduced(rtp, po):

@@ -23,9 +23,9 @@ def po_mesh(po, m):
     return po.Mesh(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], None, m["shape"]).build_boxes()
 
 
-def rtp_scene(rtp, m, pm=None):
+def rtp_scene(rtp, m, pm=None, build=0):
     kw = dict(boxes=pm.boxes, box_off=pm.box_off, box_faces=pm.box_faces) if pm is not None else {}
-    return rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], **kw)
+    return rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], build=build, **kw)
 
 
 def compare(out, o, px):
@@ -133,3 +133,22 @@ def test_c5_shape_ambient_occlusion_rays(rtp, po):
     f2, t2 = po.closest_rays(pm, rays[::4], threads=16)
     s.close()
     assert np.array_equal(g["face"], f2) and bits_equal(g["t"], t2).all()
+
+
+@pytest.mark.gpu
+def test_c3_gpu_built_bvh_equals_host_built(rtp):
+    """1 M triangles: the device-built LBVH and the host SAH tree must give the same full-HD frame
+    (face ids and float RGB bit for bit) - the hierarchy only culls."""
+    synth = synth_mod()
+    m = synth.terrain(708)
+    view = synth.look_at((0.0, 0.30, 0.20), (0.0, -0.05, -0.08))
+    w, h = 1920, 1080
+    frames = []
+    for build in (rtp.BUILD_HOST_SAH, rtp.BUILD_GPU_LBVH):
+        s = rtp_scene(rtp, m, build=build)
+        s.set_lights(synth.LIGHT_DEFAULT, None)
+        s.set_camera(w, h, view)
+        frames.append(s.render(w, h, max_depth=1, want=("rgb", "hit")))
+        s.close()
+    assert np.array_equal(frames[0]["hit"], frames[1]["hit"])
+    assert bits_equal(frames[0]["rgb"], frames[1]["rgb"]).all()
