@@ -4,6 +4,9 @@
 #include <algorithm>
 #include <atomic>
 #include <cmath>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <thread>
@@ -40,7 +43,7 @@ struct Builder {
   int32_t *idx;
   BvhNode *nodes;  // sparse: a subtree over n prims owns n-1 consecutive slots
   int max_leaf;
-  int par_depth;
+  int par_min;  // 0: single-threaded
   std::atomic<int> depth_seen{0};
 
   static int32_t leaf_code(int first, int count) { return ~((first << 3) | (count - 1)); }
@@ -77,36 +80,47 @@ struct Builder {
     int best_axis = -1, best_bin = -1;
     if (depth < kMedianDepth) {
       const float inv_area = 1.0f / std::max(box_area(whole), 1e-30f);
+      // one sweep bins every primitive on the three axes at once
+      int cnt[3][kBins] = {{0}};
+      Aabb bb[3][kBins];
+      float scale[3];
+      bool live[3];
       for (int axis = 0; axis < 3; ++axis) {
         float ext = chi[axis] - clo[axis];
-        if (!(ext > 0.f)) continue;
-        float scale = kBins * (1.0f - 1e-6f) / ext;
-        int cnt[kBins] = {0};
-        Aabb bb[kBins];
-        for (auto &b : bb) box_reset(b);
-        for (int i = l; i < r; ++i) {
-          int p = idx[i];
-          int b = (int)((cen[3 * (size_t)p + axis] - clo[axis]) * scale);
+        live[axis] = ext > 0.f;
+        scale[axis] = live[axis] ? kBins * (1.0f - 1e-6f) / ext : 0.f;
+        for (auto &b : bb[axis]) box_reset(b);
+      }
+      for (int i = l; i < r; ++i) {
+        const int p = idx[i];
+        const Aabb &pbox = pb[p];
+        const float *c = &cen[3 * (size_t)p];
+        for (int axis = 0; axis < 3; ++axis) {
+          if (!live[axis]) continue;
+          int b = (int)((c[axis] - clo[axis]) * scale[axis]);
           b = b < 0 ? 0 : (b >= kBins ? kBins - 1 : b);
-          cnt[b]++;
-          box_grow(bb[b], pb[p]);
+          cnt[axis][b]++;
+          box_grow(bb[axis][b], pbox);
         }
+      }
+      for (int axis = 0; axis < 3; ++axis) {
+        if (!live[axis]) continue;
         float rarea[kBins];
         int rcnt[kBins];
         Aabb acc;
         box_reset(acc);
         int c = 0;
         for (int b = kBins - 1; b > 0; --b) {
-          box_grow(acc, bb[b]);
-          c += cnt[b];
+          box_grow(acc, bb[axis][b]);
+          c += cnt[axis][b];
           rarea[b] = box_area(acc);
           rcnt[b] = c;
         }
         box_reset(acc);
         c = 0;
         for (int b = 0; b < kBins - 1; ++b) {
-          box_grow(acc, bb[b]);
-          c += cnt[b];
+          box_grow(acc, bb[axis][b]);
+          c += cnt[axis][b];
           if (c == 0 || rcnt[b + 1] == 0) continue;
           float cost = kCostNode + kCostTri * (c * box_area(acc) + rcnt[b + 1] * rarea[b + 1]) * inv_area;
           if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
@@ -161,7 +175,9 @@ struct Builder {
     };
     const int nl = mid - l;
     int32_t *c0 = &node.child0, *c1 = &node.child1;
-    if (depth < par_depth && r - l > 8192) {
+    // one task per subtree above par_min primitives: SAH splits are uneven, so there are several
+    // times more tasks than threads and the parent works on the other half meanwhile
+    if (par_min > 0 && nl > par_min && r - mid > par_min) {
       std::thread th(child, l, mid, slot + 1, c0);
       child(mid, r, slot + nl, c1);
       th.join();
@@ -185,6 +201,14 @@ void build_bvh(const std::vector<Aabb> &prim_bounds, int max_leaf, int n_threads
   if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
   if (n_threads <= 0) n_threads = 1;
 
+  const bool timing = std::getenv("RTP_BUILD_TIMING") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[build_bvh]     %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_prev = now;
+  };
   Builder b;
   b.pb = prim_bounds.data();
   b.cen.resize(3 * (size_t)n);
@@ -192,9 +216,9 @@ void build_bvh(const std::vector<Aabb> &prim_bounds, int max_leaf, int n_threads
     for (int k = 0; k < 3; ++k) b.cen[3 * (size_t)i + k] = 0.5f * (prim_bounds[i].lo[k] + prim_bounds[i].hi[k]);
   b.idx = out.order.data();
   b.max_leaf = max_leaf;
-  b.par_depth = 0;
-  while ((1 << b.par_depth) < n_threads) ++b.par_depth;
+  b.par_min = n_threads > 1 ? std::max(8192, n / (8 * n_threads)) : 0;
 
+  lap("centroids");
   std::vector<BvhNode> sparse((size_t)std::max(n - 1, 1));
   b.nodes = sparse.data();
   if (n == 1) {
@@ -212,6 +236,7 @@ void build_bvh(const std::vector<Aabb> &prim_bounds, int max_leaf, int n_threads
     b.build_node(0, n, mid, lb, rb, 0, 0);
   }
 
+  lap("split recursion");
   // compact the sparse array in DFS pre-order
   out.nodes.reserve((size_t)n / 2 + 1);
   struct Item { int sparse_slot; int parent; int which; int depth; };
@@ -231,6 +256,7 @@ void build_bvh(const std::vector<Aabb> &prim_bounds, int max_leaf, int n_threads
     if (nd.child1 >= 0) stack.push_back({nd.child1, me, 1, it.depth + 1}); else out.n_leaves++;
     if (nd.child0 >= 0) stack.push_back({nd.child0, me, 0, it.depth + 1}); else out.n_leaves++;
   }
+  lap("pre-order compaction");
 }
 
 }  // namespace rtp

@@ -17,15 +17,17 @@ struct RefBox {
 
 // One step of the reference algorithm, exposed so that the BoundingBox mirror class
 // (host/BoundingBox.cpp) and the array builder below share a single implementation.
-void refbox_fit_faces(RefBox &b, const float *verts, const int32_t *faces);
+void refbox_fit_faces(RefBox &b, const float *verts, const int32_t *faces, int n_threads = 1);
 bool refbox_has_face(const RefBox &b, const float *verts, const int32_t *face3);
 float refbox_average_vertex_coord(const RefBox &b, const float *verts, const int32_t *faces, int axis);
 // splitBox: returns 0 = all axes failed (nullptr), 1 = this axis failed (returns this),
 // 2 = split done, `created` holds the new box.
-int refbox_split(RefBox &b, RefBox &created, const float *verts, const int32_t *faces);
+// n_threads > 1 lets a large box cut its face sweeps into chunks; the result does not change.
+int refbox_split(RefBox &b, RefBox &created, const float *verts, const int32_t *faces, int n_threads = 1);
 
-// generateBoundingBoxes over a whole mesh. verts: V x 4, faces: F x 3.
+// generateBoundingBoxes over a whole mesh. verts: V x 4, faces: F x 3.  n_threads <= 0: all host
+// cores; the list does not depend on the thread count.
 void build_reference_boxes(const float *verts, const int32_t *faces, int n_faces, int min_faces,
-                           int max_boxes, std::vector<RefBox> &out);
+                           int max_boxes, std::vector<RefBox> &out, int n_threads = 0);
 
 }  // namespace rtp

@@ -49,7 +49,8 @@ struct DevBuf {
     if (e == cudaSuccess) n = count;
     return e;
   }
-  cudaError_t upload(const std::vector<T> &v, cudaStream_t st) {
+  template <class A>
+  cudaError_t upload(const std::vector<T, A> &v, cudaStream_t st) {
     cudaError_t e = ensure(v.size());
     if (e != cudaSuccess) return e;
     if (v.empty()) return cudaSuccess;
@@ -196,9 +197,9 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
   // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
-  std::vector<float4>().swap(h.nodes);
-  std::vector<float4>().swap(h.tris);
-  std::vector<float4>().swap(h.vnorm);
+  BigVec<float4>().swap(h.nodes);
+  BigVec<float4>().swap(h.tris);
+  BigVec<float4>().swap(h.vnorm);
   DeviceScene &d = s->dS;
   d.nodes = s->nodes.p; d.tris = s->tris.p; d.vnorm = s->vnorm.p; d.boxes = s->boxes.p;
   d.face_of = s->face_of.p; d.materials = s->materials.p; d.lights = nullptr; d.n_lights = 0;

@@ -6,8 +6,11 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+#include <chrono>
+#include <cstdio>
 #include <cstring>
 
+#include "parallel_for.h"
 #include "ref_boxes.h"
 
 namespace rtp {
@@ -26,6 +29,14 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   for (int i = 0; i < m.n_faces; ++i)
     if (m.face_mat[i] < -1 || m.face_mat[i] >= m.n_mats) return "rtp_mesh: material id out of range";
 
+  const bool timing = std::getenv("RTP_BUILD_TIMING") != nullptr;
+  auto t_prev = std::chrono::steady_clock::now();
+  auto lap = [&](const char *what) {
+    if (!timing) return;
+    auto now = std::chrono::steady_clock::now();
+    std::fprintf(stderr, "[flatten_scene] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+    t_prev = now;
+  };
   // ---- the reference's BoundingBox list (given, or built by the reference's splitter) ----
   if (m.n_boxes > 0) {
     if (!m.boxes || !m.box_off || !m.box_faces) return "rtp_mesh: n_boxes > 0 but box arrays are NULL";
@@ -40,7 +51,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   } else {
     std::vector<RefBox> rb;
     build_reference_boxes(m.verts, m.faces, m.n_faces, m.min_faces > 0 ? m.min_faces : 300,
-                          m.max_boxes > 0 ? m.max_boxes : INT32_MAX, rb);
+                          m.max_boxes > 0 ? m.max_boxes : INT32_MAX, rb, n_threads);
     out.box_bounds.clear(); out.box_off.assign(1, 0); out.box_faces.clear();
     for (const RefBox &b : rb) {
       for (int k = 0; k < 3; ++k) out.box_bounds.push_back(b.low[k]);
@@ -49,6 +60,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
       out.box_off.push_back((int32_t)out.box_faces.size());
     }
   }
+  lap("reference BoundingBox list");
   out.n_boxes = (int)out.box_off.size() - 1;
   out.boxes.resize(2 * (size_t)out.n_boxes);
   for (int b = 0; b < out.n_boxes; ++b) {
@@ -74,67 +86,88 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   const int n = (int)out.box_faces.size();
   if (n == 0) return "rtp_mesh: the BoundingBox list holds no faces";
   out.n_tris = n;
-  std::vector<float4> T((size_t)n * 4), N((size_t)n * 3);
+  BigVec<float4> T((size_t)n * 4), N((size_t)n * 3);
   std::vector<Aabb> bounds((size_t)n);
+  std::vector<int32_t> box_of_rank((size_t)n);
+  parallel_for((size_t)out.n_boxes, n_threads, 64, [&](size_t b0, size_t b1, int) {
+    for (size_t b = b0; b < b1; ++b)
+      for (int r = out.box_off[b]; r < out.box_off[b + 1]; ++r) box_of_rank[(size_t)r] = (int32_t)b;
+  });
+  // faces are independent; each thread keeps its own extent / counters, merged below
+  struct Partial {
+    float maxabs = 1.f, lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    int flagged = 0, degenerate = 0;
+  };
+  std::vector<Partial> part((size_t)host_threads(n_threads));
+  parallel_for((size_t)n, n_threads, 1 << 14, [&](size_t r0, size_t r1, int tid) {
+    Partial &acc = part[(size_t)tid];
+    for (size_t r = r0; r < r1; ++r) {
+      const int f = out.box_faces[r];
+      const int32_t *id = m.faces + 3 * (size_t)f;
+      // world vertices: M * v.head<3>() (flyscene.cpp:449,574-576)
+      v3 w[3];
+      for (int k = 0; k < 3; ++k) w[k] = affine_mul(m.shape, ld3(m.verts + 4 * (size_t)id[k]));
+      v3 fn;
+      if (m.face_normal) fn = ld3(m.face_normal + 3 * (size_t)f);
+      else {  // Mesh::createFaces, mesh.hpp:475-477 (object-space, normalised edges)
+        v3 a = ld3(m.verts + 4 * (size_t)id[0]), b = ld3(m.verts + 4 * (size_t)id[1]), c = ld3(m.verts + 4 * (size_t)id[2]);
+        v3 e1 = vnormalized_dyn(vsub(c, a));
+        v3 e0 = vnormalized_dyn(vsub(b, a));
+        fn = vnormalized(vcross(e0, e1));
+      }
+      v3 nhat = vnormalized(fn);          // face.normal.normalized(), flyscene.cpp:450,577
+      float dP = vdot(nhat, w[0]);        // :459
+      v3 vn[3];
+      for (int k = 0; k < 3; ++k) vn[k] = vnormalized(ld3(m.normals + 3 * (size_t)id[k]));  // :599
+      unsigned flags = 0;
+      bool unit = true;
+      for (int k = 0; k < 3; ++k) {
+        float q = vdot(vn[k], vn[k]);
+        if (!(q > 0.5f && q < 1.5f)) unit = false;
+      }
+      if (!unit || !(vdot(vn[0], vn[1]) >= -0.49f) || !(vdot(vn[1], vn[2]) >= -0.49f) || !(vdot(vn[0], vn[2]) >= -0.49f)) {
+        flags |= kTriFlagNormalCheck;
+        acc.flagged++;
+      }
+      float nq = vdot(nhat, nhat);
+      if (!(nq > 0.5f && nq < 1.5f)) acc.degenerate++;
+      unsigned mat = (unsigned)(m.face_mat[f] + 1);
+      T[4 * r + 0] = f4(w[0], i2f((int)r));
+      T[4 * r + 1] = f4(w[1], i2f(box_of_rank[r]));
+      T[4 * r + 2] = f4(w[2], i2f((int)(mat | flags)));
+      T[4 * r + 3] = f4(nhat, dP);
+      for (int k = 0; k < 3; ++k) N[3 * r + k] = f4(vn[k], 0.f);
+      Aabb &bb = bounds[r];
+      bool finite = true;
+      for (int a = 0; a < 3; ++a) {
+        float c0 = (&w[0].x)[a], c1 = (&w[1].x)[a], c2 = (&w[2].x)[a];
+        if (!std::isfinite(c0) || !std::isfinite(c1) || !std::isfinite(c2)) finite = false;
+        bb.lo[a] = std::min(c0, std::min(c1, c2));
+        bb.hi[a] = std::max(c0, std::max(c1, c2));
+        if (finite) acc.maxabs = std::max(acc.maxabs, std::max(std::fabs(bb.lo[a]), std::fabs(bb.hi[a])));
+      }
+      if (finite)
+        for (int a = 0; a < 3; ++a) {
+          acc.lo[a] = std::min(acc.lo[a], bb.lo[a]);
+          acc.hi[a] = std::max(acc.hi[a], bb.hi[a]);
+        }
+      if (!finite)
+        for (int a = 0; a < 3; ++a) { bb.lo[a] = -FLT_MAX; bb.hi[a] = FLT_MAX; }
+    }
+  });
   float maxabs = 1.f;
   for (int a = 0; a < 3; ++a) { out.scene_lo[a] = FLT_MAX; out.scene_hi[a] = -FLT_MAX; }
   out.n_flagged = out.n_degenerate = 0;
-  std::vector<int32_t> box_of_rank((size_t)n);
-  for (int b = 0; b < out.n_boxes; ++b)
-    for (int r = out.box_off[b]; r < out.box_off[b + 1]; ++r) box_of_rank[(size_t)r] = b;
-  for (int r = 0; r < n; ++r) {
-    const int f = out.box_faces[(size_t)r];
-    const int32_t *id = m.faces + 3 * (size_t)f;
-    // world vertices: M * v.head<3>() (flyscene.cpp:449,574-576)
-    v3 w[3];
-    for (int k = 0; k < 3; ++k) w[k] = affine_mul(m.shape, ld3(m.verts + 4 * (size_t)id[k]));
-    v3 fn;
-    if (m.face_normal) fn = ld3(m.face_normal + 3 * (size_t)f);
-    else {  // Mesh::createFaces, mesh.hpp:475-477 (object-space, normalised edges)
-      v3 a = ld3(m.verts + 4 * (size_t)id[0]), b = ld3(m.verts + 4 * (size_t)id[1]), c = ld3(m.verts + 4 * (size_t)id[2]);
-      v3 e1 = vnormalized_dyn(vsub(c, a));
-      v3 e0 = vnormalized_dyn(vsub(b, a));
-      fn = vnormalized(vcross(e0, e1));
-    }
-    v3 nhat = vnormalized(fn);          // face.normal.normalized(), flyscene.cpp:450,577
-    float dP = vdot(nhat, w[0]);        // :459
-    v3 vn[3];
-    for (int k = 0; k < 3; ++k) vn[k] = vnormalized(ld3(m.normals + 3 * (size_t)id[k]));  // :599
-    unsigned flags = 0;
-    bool unit = true;
-    for (int k = 0; k < 3; ++k) {
-      float q = vdot(vn[k], vn[k]);
-      if (!(q > 0.5f && q < 1.5f)) unit = false;
-    }
-    if (!unit || !(vdot(vn[0], vn[1]) >= -0.49f) || !(vdot(vn[1], vn[2]) >= -0.49f) || !(vdot(vn[0], vn[2]) >= -0.49f)) {
-      flags |= kTriFlagNormalCheck;
-      out.n_flagged++;
-    }
-    float nq = vdot(nhat, nhat);
-    if (!(nq > 0.5f && nq < 1.5f)) out.n_degenerate++;
-    unsigned mat = (unsigned)(m.face_mat[f] + 1);
-    T[4 * (size_t)r + 0] = f4(w[0], i2f(r));
-    T[4 * (size_t)r + 1] = f4(w[1], i2f(box_of_rank[(size_t)r]));
-    T[4 * (size_t)r + 2] = f4(w[2], i2f((int)(mat | flags)));
-    T[4 * (size_t)r + 3] = f4(nhat, dP);
-    for (int k = 0; k < 3; ++k) N[3 * (size_t)r + k] = f4(vn[k], 0.f);
-    Aabb &bb = bounds[(size_t)r];
-    bool finite = true;
+  for (const Partial &acc : part) {
+    maxabs = std::max(maxabs, acc.maxabs);
     for (int a = 0; a < 3; ++a) {
-      float c0 = (&w[0].x)[a], c1 = (&w[1].x)[a], c2 = (&w[2].x)[a];
-      if (!std::isfinite(c0) || !std::isfinite(c1) || !std::isfinite(c2)) finite = false;
-      bb.lo[a] = std::min(c0, std::min(c1, c2));
-      bb.hi[a] = std::max(c0, std::max(c1, c2));
-      if (finite) maxabs = std::max(maxabs, std::max(std::fabs(bb.lo[a]), std::fabs(bb.hi[a])));
+      out.scene_lo[a] = std::min(out.scene_lo[a], acc.lo[a]);
+      out.scene_hi[a] = std::max(out.scene_hi[a], acc.hi[a]);
     }
-    if (finite)
-      for (int a = 0; a < 3; ++a) {
-        out.scene_lo[a] = std::min(out.scene_lo[a], bb.lo[a]);
-        out.scene_hi[a] = std::max(out.scene_hi[a], bb.hi[a]);
-      }
-    if (!finite)
-      for (int a = 0; a < 3; ++a) { bb.lo[a] = -FLT_MAX; bb.hi[a] = FLT_MAX; }
+    out.n_flagged += acc.flagged;
+    out.n_degenerate += acc.degenerate;
   }
+  lap("per-face flatten");
   // Conservative padding: the exact test accepts points P = o + t*d that carry a few ulps of
   // rounding at |o| + t, so a face may be "hit" by a ray that misses its tight box by ~1e-6.
   float pad_rel = 3e-5f;
@@ -146,7 +179,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
     out.nodes.clear();
     out.tris.swap(T);
     out.vnorm.swap(N);
-    out.face_of = out.box_faces;
+    out.face_of.assign(out.box_faces.begin(), out.box_faces.end());
     return "";
   }
   for (Aabb &bb : bounds)
@@ -157,6 +190,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   int max_leaf = 4;
   if (const char *e = std::getenv("RTP_BVH_MAX_LEAF")) max_leaf = std::atoi(e);
   build_bvh(bounds, max_leaf, n_threads, bvh);
+  lap("binned-SAH BVH");
   if (bvh.max_depth >= kStackSize - 2) return "BVH deeper than the traversal stack";
   out.bvh_depth = bvh.max_depth;
   out.n_nodes = (int)bvh.nodes.size();
@@ -166,12 +200,15 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   out.tris.resize((size_t)n * 4);
   out.vnorm.resize((size_t)n * 3);
   out.face_of.resize((size_t)n);
-  for (int s = 0; s < n; ++s) {
-    const int r = bvh.order[(size_t)s];
-    for (int k = 0; k < 4; ++k) out.tris[4 * (size_t)s + k] = T[4 * (size_t)r + k];
-    for (int k = 0; k < 3; ++k) out.vnorm[3 * (size_t)s + k] = N[3 * (size_t)r + k];
-    out.face_of[(size_t)s] = out.box_faces[(size_t)r];
-  }
+  parallel_for((size_t)n, n_threads, 1 << 14, [&](size_t s0, size_t s1, int) {
+    for (size_t s = s0; s < s1; ++s) {
+      const size_t r = (size_t)bvh.order[s];
+      for (int k = 0; k < 4; ++k) out.tris[4 * s + k] = T[4 * r + k];
+      for (int k = 0; k < 3; ++k) out.vnorm[3 * s + k] = N[3 * r + k];
+      out.face_of[s] = out.box_faces[r];
+    }
+  });
+  lap("leaf-order permutation");
   return "";
 }
 

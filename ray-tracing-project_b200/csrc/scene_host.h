@@ -2,7 +2,9 @@
 // (rtp_device.h) plus the BVH over it.  Pure C++ (no CUDA) so tests/hostsim can reuse it.
 #pragma once
 #include <cstdint>
+#include <memory>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/rtp.h"
@@ -11,12 +13,23 @@
 
 namespace rtp {
 
+// std::vector whose resize() leaves trivially-constructible elements uninitialised: the per-triangle
+// arrays are hundreds of MB and every element is written by the (threaded) loops that follow, so a
+// single-threaded zero fill would only serialise the first touch of those pages.
+template <class T>
+struct DefaultInit : std::allocator<T> {
+  template <class U> struct rebind { using other = DefaultInit<U>; };
+  template <class U> void construct(U *p) noexcept(noexcept(::new ((void *)p) U)) { ::new ((void *)p) U; }
+  template <class U, class... A> void construct(U *p, A &&...a) { ::new ((void *)p) U(std::forward<A>(a)...); }
+};
+template <class T> using BigVec = std::vector<T, DefaultInit<T>>;
+
 struct HostScene {
-  std::vector<float4> nodes;      // 4 per node
-  std::vector<float4> tris;       // 4 per triangle, leaf order
-  std::vector<float4> vnorm;      // 3 per triangle, leaf order
+  BigVec<float4> nodes;           // 4 per node
+  BigVec<float4> tris;            // 4 per triangle, leaf order
+  BigVec<float4> vnorm;           // 3 per triangle, leaf order
   std::vector<float4> boxes;      // 2 per reference box
-  std::vector<int32_t> face_of;   // slot -> face id
+  BigVec<int32_t> face_of;        // slot -> face id
   std::vector<float4> materials;  // 3 per entry, entry 0 = Flyscene defaults (material_id -1)
   float minv[12];
   // reference BoundingBox list (kept for rtp_scene_get_boxes)

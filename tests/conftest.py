@@ -105,6 +105,14 @@ class HostSimScene:
                                  bf.ctypes.data_as(C.c_void_p))
         return bb, off, bf
 
+    def layout(self):
+        """Device layout as flatten_scene made it: BVH nodes, triangles in leaf order, slot -> face id."""
+        nn, nt = self.info["n_nodes"], self.info["n_tris"]
+        nodes, tris, face_of = np.zeros((nn, 16), np.float32), np.zeros((nt, 16), np.float32), np.zeros(nt, np.int32)
+        vp = lambda a: a.ctypes.data_as(C.c_void_p)
+        self.H.hostsim_get_layout(self.h, vp(nodes), vp(tris), vp(face_of))
+        return nodes, tris, face_of
+
     def render(self, w, h, view, max_depth, point, dirl, pixels=None):
         import pyoracle
         l, keep = self.rtp.make_lights_struct(point, dirl)

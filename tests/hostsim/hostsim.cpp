@@ -8,6 +8,7 @@
 // that GPU minutes are spent on measuring rather than on debugging host logic.
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -28,7 +29,8 @@ struct hostsim_scene {
 const char *hostsim_create(const rtp_mesh *m, hostsim_scene **out) {
   static std::string err;
   hostsim_scene *s = new hostsim_scene();
-  err = flatten_scene(*m, s->h, 1);
+  const char *nt = std::getenv("HOSTSIM_THREADS");  // the build must not depend on the thread count
+  err = flatten_scene(*m, s->h, nt ? std::atoi(nt) : 1);
   if (!err.empty()) { delete s; return err.c_str(); }
   DeviceScene &d = s->d;
   d.nodes = s->h.nodes.data(); d.tris = s->h.tris.data(); d.vnorm = s->h.vnorm.data();
@@ -48,6 +50,11 @@ void hostsim_get_boxes(hostsim_scene *s, float *b, int *off, int *faces) {
   std::memcpy(b, s->h.box_bounds.data(), s->h.box_bounds.size() * 4);
   std::memcpy(off, s->h.box_off.data(), s->h.box_off.size() * 4);
   std::memcpy(faces, s->h.box_faces.data(), s->h.box_faces.size() * 4);
+}
+void hostsim_get_layout(hostsim_scene *s, float *nodes /* 16 per node */, float *tris /* 16 per tri */, int *face_of) {
+  std::memcpy(nodes, s->h.nodes.data(), s->h.nodes.size() * sizeof(float4));
+  std::memcpy(tris, s->h.tris.data(), s->h.tris.size() * sizeof(float4));
+  std::memcpy(face_of, s->h.face_of.data(), s->h.face_of.size() * 4);
 }
 void hostsim_set_lights(hostsim_scene *s, const rtp_lights *l) {
   pack_lights(*l, s->lights);

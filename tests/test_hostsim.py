@@ -106,3 +106,33 @@ def test_tile_tables_partition_the_image(hostsim):
             assert np.array_equal(loc[own], np.arange(n.value))
             assert abs(n.value - tx * ty / world) <= max(tx, ty)
         assert (seen == 1).all()
+
+
+def test_scene_build_does_not_depend_on_the_thread_count(hostsim, rtp, po, monkeypatch):
+    """The threaded host build (BoundingBox passes split concurrently, large boxes swept in chunks,
+    per-face flatten and BVH subtrees as tasks) must produce, bit for bit, the arrays the
+    single-threaded build produces - and the BoundingBox list of the oracle's sequential splitter.
+    80 000 faces: the first passes take the chunked path (ref_boxes.cpp kChunkedSplitMin)."""
+    import importlib
+    from types import SimpleNamespace
+    synth = importlib.import_module("ray-tracing-project_b200.synth")
+    d = synth.terrain(200)
+    # a NaN vertex and signed zeros: the min/max merge has to treat them like the sequential loop
+    d["verts"][7, 1] = np.nan
+    d["verts"][:3, 2] = np.float32(-0.0)
+    m = SimpleNamespace(**d)
+    built = []
+    for threads in ("1", "8", "3"):
+        monkeypatch.setenv("HOSTSIM_THREADS", threads)
+        s = HostSimScene(hostsim, rtp, m)
+        built.append((s.info, s.boxes(), s.layout()))
+        s.close()
+    ref = built[0]
+    assert ref[0]["n_boxes"] > 300
+    for info, boxes, layout in built[1:]:
+        assert info == ref[0]
+        for a, b in zip(boxes + layout, ref[1] + ref[2]):
+            assert a.shape == b.shape and np.array_equal(a.view(np.int32), b.view(np.int32))
+    pm = po.Mesh(d["verts"], d["normals"], d["faces"], d["face_mat"], d["materials"], None, d["shape"]).build_boxes()
+    bb, off, bf = ref[1]
+    assert np.array_equal(off, pm.box_off) and np.array_equal(bf, pm.box_faces) and bits_equal(bb, pm.boxes).all()
