@@ -301,19 +301,33 @@ def run_ours(args, wl, rtp):
         flush.zero_()          # evict the scene from L2 between timed iterations (untimed)
         sync_all()
         ev0.record()
-        step(profile=True)     # per-kernel CUDA events are recorded on the launch stream, read after the sync
+        step()
         ev1.record()
         sync_all()
         t = torch.tensor([ev0.elapsed_time(ev1)], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_steps.append(float(t.item()))
+    clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
+    fs = scene.frame_stats()
+    groups = scene.tile_groups()
+    launches_rank0 = (fs["kernel_launches"] + (0 if peer else 1)) * args.steps  # frame kernels (+ un-tile on rank 0)
+    # per-kernel durations: the same steps once more with RTP_RENDER_PROFILE, which brackets every launch with
+    # CUDA events on the launch stream; the tile groups then run one after the other, so that an event pair
+    # times one kernel alone (in the timed region above kernels of different groups overlap)
+    ms_serial = []
+    for _ in range(args.steps):
+        flush.zero_()
+        sync_all()
+        ev0.record()
+        step(profile=True)
+        ev1.record()
+        sync_all()
+        ms_serial.append(ev0.elapsed_time(ev1))
         fs = scene.frame_stats()
         k_closest.append(fs["ms_closest"])
         k_any.append(fs["ms_anyhit"])
         k_shade.append(fs["ms_shade"])
-    clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
-    launches_rank0 = (fs["kernel_launches"] + (0 if peer else 1)) * args.steps  # frame kernels (+ un-tile on rank 0)
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
     e2e_ms = []
@@ -368,6 +382,7 @@ def run_ours(args, wl, rtp):
                                         if peer else "NCCL gather of tile buffers + un-tile kernel") if world > 1 else
                                        "resolve kernel writes the image (1 GPU)" if peer else "un-tile kernel (1 GPU)",
                                 peer_image_equals_nccl_gather=same,
+                                tile_groups=f"{groups} bands of this rank's tiles, each on its own CUDA stream",
                                 l2="256 MiB memset between timed steps (untimed) flushes the 126 MB L2",
                                 scene_build_s=round(t_build, 2)),
                     clocks=clocks,
@@ -381,6 +396,8 @@ def run_ours(args, wl, rtp):
                                   alg_bytes_per_ray=b_alg(n_tris),
                                   peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
                                   kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
+                                  kernels_ms_from=f"{args.steps} more steps with per-kernel CUDA events, tile groups "
+                                                  f"serialised: {float(np.mean(ms_serial)):.4f} ms per step",
                                   issue=dict(note="traversal is issue/latency bound, not DRAM bound: see profiles/",
                                              grays_per_s_kernel=dom_rays / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0)))
         if world == 1 and not args.no_cpu_baseline:

@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 3
+#define RTP_ABI_VERSION 4
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -114,6 +114,13 @@ int rtp_scene_destroy(rtp_scene *s); /* ~Flyscene / BoundingBox::deconstruct */
 int rtp_set_lights(rtp_scene *s, const rtp_lights *l);
 /* getCamera()->setViewport / setPerspectiveMatrix / view matrix (flyscene.cpp:14-15). */
 int rtp_set_camera(rtp_scene *s, const rtp_camera *c);
+
+/* Tuning knob with no counterpart in the reference (its 20 row-band threads, flyscene.cpp:266-285, are the
+ * nearest relative): a frame's owned tiles are cut into `groups` bands that run as independent sub-frames
+ * on their own CUDA streams, so that one band's kernels fill the idle tail of another's.  0 = automatic
+ * (default), 1 = one launch sequence for the whole frame, at most 8.  The image does not depend on it. */
+int rtp_set_tile_groups(rtp_scene *s, int groups);
+int rtp_get_tile_groups(const rtp_scene *s); /* bands the most recently enqueued frame was cut into */
 
 /* ---- the render entry point --------------------------------------------------------------- */
 /* Replaces Flyscene::raytraceScene + traceRayThread (flyscene.cpp:250-314) for the full

@@ -61,7 +61,7 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
+           "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
            "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free"]
 
 _lib = None
@@ -86,6 +86,8 @@ def lib():
         L.rtp_scene_destroy.argtypes = [C.c_void_p]
         L.rtp_set_lights.argtypes = [C.c_void_p, C.POINTER(RtpLights)]
         L.rtp_set_camera.argtypes = [C.c_void_p, C.POINTER(RtpCamera)]
+        L.rtp_set_tile_groups.argtypes = [C.c_void_p, C.c_int]
+        L.rtp_get_tile_groups.argtypes = [C.c_void_p]
         L.rtp_render.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.POINTER(RtpStats)]
         L.rtp_render_tiles_device.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p,
@@ -214,6 +216,13 @@ class Scene:
     def set_camera(self, w, h, view=None, fovy=60.0, aspect=None, viewport=None):
         c = make_camera_struct(w, h, view, fovy, aspect, viewport)
         self._check(self._L.rtp_set_camera(self._h, C.byref(c)))
+
+    def set_tile_groups(self, groups):
+        """rtp_set_tile_groups: bands of the frame that run on their own streams (0 = automatic)."""
+        self._check(self._L.rtp_set_tile_groups(self._h, int(groups)))
+
+    def tile_groups(self):
+        return int(self._L.rtp_get_tile_groups(self._h))
 
     def info(self):
         st = RtpStats()

@@ -58,6 +58,8 @@ struct DevBuf {
   }
 };
 
+constexpr int kMaxGroups = 8;
+
 struct Frame {
   int width = 0, height = 0, rank = 0, world = 1, max_depth = 0;
   int n_px = 0, tiles_x = 0;
@@ -87,9 +89,20 @@ struct rtp_scene {
   LaunchCfg cfg;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  // tile groups of a frame run on their own streams (enqueue_frame): group 0 on the caller's stream
+  cudaStream_t gstream[kMaxGroups] = {};
+  cudaEvent_t gfork = nullptr, gjoin[kMaxGroups] = {};
+  int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
+  int last_groups = 1;  // groups of the most recently enqueued frame (their counters are summed)
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
   std::vector<int> kev_kind;     // 0 closest, 1 anyhit, 2 streaming (raygen/prep/accum/resolve)
   int kev_used = 0;
+  // RTP_TIMELINE=1 (profiling runs): an event after every launch on the launching stream; rtp_frame_stats prints
+  // each kernel's end time relative to the start of the frame (which kernels of different groups overlapped)
+  int timeline = 0;
+  std::vector<cudaEvent_t> tev;
+  std::vector<std::string> tev_name;
+  int tev_used = 0;
   int last_primary = 0, last_depth = 0, last_lights = 0;
   cudaStream_t last_stream = nullptr;  // stream of the most recently enqueued frame
   bool has_last = false;
@@ -162,6 +175,13 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return cleanup(e, "cudaStreamCreate");
   for (auto &ev : s->ev)
     if ((e = cudaEventCreate(&ev)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
+  for (int i = 1; i < kMaxGroups; ++i)
+    if ((e = cudaStreamCreateWithFlags(&s->gstream[i], cudaStreamNonBlocking)) != cudaSuccess) return cleanup(e, "cudaStreamCreate");
+  if ((e = cudaEventCreateWithFlags(&s->gfork, cudaEventDisableTiming)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
+  for (int i = 1; i < kMaxGroups; ++i)
+    if ((e = cudaEventCreateWithFlags(&s->gjoin[i], cudaEventDisableTiming)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
+  if (const char *te = std::getenv("RTP_TIMELINE")) s->timeline = std::atoi(te);
+  if (const char *ge = std::getenv("RTP_GROUPS")) s->groups = std::min(std::max(std::atoi(ge), 0), kMaxGroups);
   HostScene &h = s->host;
   if (gpu_build) {
     // rank-ordered triangles go up once; the device sorts them, builds the hierarchy and permutes
@@ -193,8 +213,8 @@ int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
   }
   if ((e = s->boxes.upload(h.boxes, s->stream)) != cudaSuccess) return cleanup(e, "upload boxes");
   if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
-  if ((e = s->counters.ensure(kCtrInts)) != cudaSuccess) return cleanup(e, "alloc counters");
-  if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
+  if ((e = s->counters.ensure(kCtrInts * kMaxGroups)) != cudaSuccess) return cleanup(e, "alloc counters");
+  if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * kMaxGroups * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
   if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
   // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
   BigVec<float4>().swap(h.nodes);
@@ -228,6 +248,12 @@ int rtp_scene_destroy(rtp_scene *s) {
   for (auto &ev : s->ev)
     if (ev) cudaEventDestroy(ev);
   for (auto &ev : s->kev) cudaEventDestroy(ev);
+  for (auto &ev : s->tev) cudaEventDestroy(ev);
+  for (int i = 1; i < kMaxGroups; ++i) {
+    if (s->gstream[i]) { cudaStreamSynchronize(s->gstream[i]); cudaStreamDestroy(s->gstream[i]); }
+    if (s->gjoin[i]) cudaEventDestroy(s->gjoin[i]);
+  }
+  if (s->gfork) cudaEventDestroy(s->gfork);
   delete s;  // DevBuf destructors free device memory while the device is current
   return RTP_OK;
 }
@@ -246,6 +272,14 @@ int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
   s->have_lights = true;
   return RTP_OK;
 }
+
+int rtp_set_tile_groups(rtp_scene *s, int groups) {
+  if (!s || groups < 0 || groups > kMaxGroups) return fail(RTP_ERR_INVALID, "rtp_set_tile_groups: groups must be in [0, 8]");
+  s->groups = groups;
+  return RTP_OK;
+}
+
+int rtp_get_tile_groups(const rtp_scene *s) { return s ? s->last_groups : 0; }
 
 int rtp_set_camera(rtp_scene *s, const rtp_camera *c) {
   if (!s || !c) return fail(RTP_ERR_INVALID, "rtp_set_camera: null argument");
@@ -347,12 +381,66 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
   p.counters = s->counters.p;
 }
 
-// Enqueues one frame: raygen, then per level closest / prep / anyhit / accum, then resolve.
-// profile: bracket every kernel with CUDA events (summed per kernel kind by read_stats).
-int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile, int n_primary) {
+// Tile groups.  The frame's owned tiles are cut into G contiguous groups (whole tile rows on one GPU, so a
+// group is a horizontal band of the image); every group is an independent sub-frame - its own slice of every
+// path buffer, its own counter block, its own share of the parked-ray list - and runs on its own stream.
+// Each trace kernel ends in a latency-bound tail (the last batches of dependent node fetches leave most of
+// the SMs idle); with G groups in flight the tail of one group's kernel is filled by the next group's work,
+// and at the deep bounce levels, where a launch holds only a few thousand rays, the groups' small launches
+// overlap instead of queueing behind each other.  Pixels never interact, so the image does not depend on G.
+// Automatic choice, measured on B200 (profiles/r01_groups.md): three bands are best or within 1.5 % of the
+// best on every workload (C3 0.826 -> 0.764 ms, C2 0.639 -> 0.621, C4 5.19 -> 4.5); more bands only add
+// launches.  A band keeps at least 64 tiles (65 536 pixels) so that its trace launches still fill the GPU once.
+int auto_groups(const FrameParams &p) {
+  const int n_tiles = p.n_px / kTilePixels;
+  return std::max(1, std::min(3, n_tiles / 64));
+}
+
+void plan_groups(const FrameParams &p, int world, int want, int *tile0 /* G + 1 */, int *n_groups) {
+  const int n_tiles = p.n_px / kTilePixels;
+  int G = (p.tile_ids && !p.user_rays) ? std::min(want, kMaxGroups) : 1;
+  const int unit = world == 1 ? std::max(p.tiles_x, 1) : 1;  // one GPU: cut at tile-row boundaries
+  const int units = (n_tiles + unit - 1) / unit;
+  G = std::max(1, std::min(G, units));
+  for (int g = 0; g <= G; ++g) tile0[g] = std::min(n_tiles, (int)((long long)units * g / G) * unit);
+  tile0[G] = n_tiles;
+  *n_groups = G;
+}
+
+FrameParams group_params(const FrameParams &p, int g, int t0, int t1) {
+  FrameParams q = p;
+  const size_t base = (size_t)t0 * kTilePixels;
+  q.n_px = (t1 - t0) * kTilePixels;
+  q.tile_ids = p.tile_ids + t0;
+  if (p.fb) q.fb = p.fb + base;
+  q.primface = p.primface + base;
+  q.ksdeep = p.ksdeep + base;
+  q.direct = p.direct + base * (size_t)p.max_depth;  // [max_depth][group pixels]
+  for (int i = 0; i < 2; ++i) { q.ray_o[i] = p.ray_o[i] + base; q.ray_d[i] = p.ray_d[i] + base; }
+  q.hit_t = p.hit_t + base;
+  q.hit_slot = p.hit_slot + base;
+  q.hitlist = p.hitlist + base;
+  q.pbuf = p.pbuf + base;
+  q.nbuf = p.nbuf + base;
+  q.occl = p.occl + base * (size_t)std::max(p.S.n_lights, 1);
+  q.counters = p.counters + g * kCtrInts;
+  return q;
+}
+
+// Enqueues one frame: raygen, then per level closest / prep / anyhit / accum, then resolve - per tile group,
+// group 0 on `st`, the others on the scene's group streams, forked from and joined back into `st`.
+// profile: bracket every kernel with CUDA events (summed per kernel kind by read_stats); the frame then runs as
+// ONE group, so that an event pair times one kernel alone on the GPU with the whole frame's rays of that level.
+// after_group (optional): called once per group with its tile range and stream right after its resolve kernel
+// (rtp_render starts the device-to-host copy of the band there).
+template <class AfterGroup>
+int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile, int n_primary,
+                  int world, AfterGroup after_group) {
   // one frame at a time per scene: counters and path buffers are shared between frames
   if (s->has_last && s->last_stream != st) CK(cudaStreamSynchronize(s->last_stream));
-  CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * sizeof(int), st));
+  int tile0[kMaxGroups + 1], G = 1;
+  plan_groups(p, world, profile ? 1 : s->groups > 0 ? s->groups : auto_groups(p), tile0, &G);
+  CK(cudaMemsetAsync(s->counters.p, 0, (size_t)kCtrInts * G * sizeof(int), st));
   int n = 0;
   s->kev_used = 0;
   s->kev_kind.clear();
@@ -367,25 +455,69 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     s->kev_kind.push_back(kind);
     return cudaEventRecord(s->kev[s->kev_used++], st);
   };
-  CK(mark(2)); launch_raygen(p, st); ++n;
-  for (int d = 0; d < p.max_depth; ++d) {
-    CK(mark(0)); n += launch_closest(p, d, s->cfg, st);
-    CK(mark(2)); launch_prep(p, d, st);
-    CK(mark(1)); n += launch_anyhit(p, d, s->cfg, st);
-    CK(mark(2)); launch_accum(p, d, st);
-    n += 2;
+  s->tev_used = 0;
+  s->tev_name.clear();
+  auto stamp = [&](const char *what, int g, int d, cudaStream_t on) -> cudaError_t {
+    if (!s->timeline || profile) return cudaSuccess;
+    if (s->tev_used == (int)s->tev.size()) {
+      cudaEvent_t e;
+      cudaError_t err = cudaEventCreate(&e);
+      if (err != cudaSuccess) return err;
+      s->tev.push_back(e);
+    }
+    s->tev_name.push_back(std::string(what) + " g" + std::to_string(g) + " d" + std::to_string(d));
+    return cudaEventRecord(s->tev[s->tev_used++], on);
+  };
+  FrameParams gp[kMaxGroups];
+  LaunchCfg gc[kMaxGroups];
+  cudaStream_t gs[kMaxGroups];
+  for (int g = 0; g < G; ++g) {
+    gp[g] = G == 1 ? p : group_params(p, g, tile0[g], tile0[g + 1]);
+    gc[g] = s->cfg;
+    gc[g].park_cap = s->cfg.park_cap / G;
+    gc[g].park_slots = s->cfg.park_slots + (size_t)g * gc[g].park_cap * (kParkSlotBytes / sizeof(int));
+    gs[g] = g == 0 ? st : s->gstream[g];
   }
-  CK(mark(2)); launch_resolve(p, st); ++n;
+  const bool fork = G > 1 && !profile;
+  if (fork) {
+    CK(cudaEventRecord(s->gfork, st));
+    for (int g = 1; g < G; ++g) CK(cudaStreamWaitEvent(gs[g], s->gfork, 0));
+  }
+  CK(stamp("start", 0, 0, st));
+  // launches are issued phase by phase across the groups, so that the groups advance together
+  for (int g = 0; g < G; ++g) { CK(mark(2)); launch_raygen(gp[g], gs[g]); ++n; CK(stamp("raygen", g, 0, gs[g])); }
+  for (int d = 0; d < p.max_depth; ++d) {
+    for (int g = 0; g < G; ++g) { CK(mark(0)); n += launch_closest(gp[g], d, gc[g], gs[g]); CK(stamp("closest", g, d, gs[g])); }
+    for (int g = 0; g < G; ++g) { CK(mark(2)); launch_prep(gp[g], d, gs[g]); ++n; CK(stamp("prep", g, d, gs[g])); }
+    for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit(gp[g], d, gc[g], gs[g]); CK(stamp("anyhit", g, d, gs[g])); }
+    for (int g = 0; g < G; ++g) { CK(mark(2)); launch_accum(gp[g], d, gs[g]); ++n; CK(stamp("accum", g, d, gs[g])); }
+  }
+  for (int g = 0; g < G; ++g) {
+    CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
+    CK(stamp("resolve", g, 0, gs[g]));
+    CK(after_group(g, tile0[g], tile0[g + 1], gs[g]));
+  }
   CK(mark(-1));
   CK(cudaGetLastError());
+  if (fork)
+    for (int g = 1; g < G; ++g) {
+      CK(cudaEventRecord(s->gjoin[g], gs[g]));
+      CK(cudaStreamWaitEvent(st, s->gjoin[g], 0));
+    }
   s->last_stream = st;
   s->has_last = true;
   s->last_launches = n;
   s->last_primary = n_primary;
   s->last_depth = p.max_depth;
   s->last_lights = p.S.n_lights;
+  s->last_groups = G;
   if (launches) *launches = n;
   return RTP_OK;
+}
+int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *launches, bool profile, int n_primary,
+                  int world) {
+  return enqueue_frame(s, p, st, launches, profile, n_primary, world,
+                       [](int, int, int, cudaStream_t) { return cudaSuccess; });
 }
 
 int check_render_args(rtp_scene *s, const rtp_render_opts *o) {
@@ -400,9 +532,12 @@ int check_render_args(rtp_scene *s, const rtp_render_opts *o) {
 }
 
 int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
-  int h[kCtrInts];
-  CK(cudaMemcpyAsync(h, s->counters.p, sizeof h, cudaMemcpyDeviceToHost, stream));
+  int hg[kCtrInts * kMaxGroups], h[kCtrInts] = {};
+  const int G = std::min(std::max(s->last_groups, 1), kMaxGroups);
+  CK(cudaMemcpyAsync(hg, s->counters.p, (size_t)kCtrInts * G * sizeof(int), cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
+  for (int g = 0; g < G; ++g)
+    for (int i = 0; i < kCtrInts; ++i) h[i] += hg[g * kCtrInts + i];
   for (int i = 0; i + 1 < s->kev_used; ++i) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, s->kev[i], s->kev[i + 1]));
@@ -433,6 +568,14 @@ int rtp_frame_stats(rtp_scene *s, rtp_stats *st) {
   int rc = read_stats(s, st, s->has_last ? s->last_stream : s->stream);
   if (rc) return rc;
   st->kernel_launches = s->last_launches;
+  if (s->timeline && s->tev_used > 1) {
+    std::fprintf(stderr, "rtp timeline (ms after frame start, end of each launch):\n");
+    for (int i = 1; i < s->tev_used; ++i) {
+      float ms = 0.f;
+      if (cudaEventSynchronize(s->tev[i]) != cudaSuccess || cudaEventElapsedTime(&ms, s->tev[0], s->tev[i]) != cudaSuccess) continue;
+      std::fprintf(stderr, "  %-16s %8.4f\n", s->tev_name[(size_t)i].c_str(), ms);
+    }
+  }
   return RTP_OK;
 }
 
@@ -466,7 +609,7 @@ int rtp_render_tiles_device(rtp_scene *s, const rtp_render_opts *o, void *d_tile
   fill_params(s, f, *o, (float4 *)d_tiles, p);
   int launches = 0;
   if (st) CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid, o->world);
   if (rc) return rc;
   if (st) {
     CK(cudaEventRecord(s->ev[1], cs));
@@ -497,7 +640,7 @@ int rtp_render_image_device(rtp_scene *s, const rtp_render_opts *o, void *d_rgb8
   p.img_hit = (int *)d_hit;
   int launches = 0;
   if (st) CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid, o->world);
   if (rc) return rc;
   if (st) {
     CK(cudaEventRecord(s->ev[1], cs));
@@ -594,9 +737,40 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   }
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid);
+  // one GPU, finished planes written by the resolve kernel: a tile group is a band of image rows, and its
+  // device-to-host copy starts on the group's stream as soon as that band is resolved, under the other
+  // groups' kernels
+  const bool banded = fused && o->world == 1;
+  const int tiles_x = f.tiles_x, width = o->width, height = o->height;
+  unsigned char *d_rgb8 = f.out_rgb8.p;
+  int *d_hit = f.out_hit.p;
+  auto copy_band = [=](int, int t0, int t1, cudaStream_t gs) -> cudaError_t {
+    if (!banded || t1 <= t0) return cudaSuccess;
+    const size_t y0 = (size_t)(t0 / tiles_x) * kTileDim;
+    const size_t y1 = std::min<size_t>((size_t)height, (size_t)((t1 + tiles_x - 1) / tiles_x) * kTileDim);
+    if (y1 <= y0) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    if (rgb8) e = cudaMemcpyAsync(rgb8 + y0 * width * 3, d_rgb8 + y0 * width * 3, (y1 - y0) * width * 3, cudaMemcpyDeviceToHost, gs);
+    if (e == cudaSuccess && hit)
+      e = cudaMemcpyAsync(hit + y0 * width, d_hit + y0 * width, (y1 - y0) * width * sizeof(int), cudaMemcpyDeviceToHost, gs);
+    return e;
+  };
+  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid, o->world, copy_band);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
+  if (banded) {
+    CK(cudaEventRecord(s->ev[2], cs));
+    CK(cudaStreamSynchronize(cs));
+    if (st) {
+      std::memset(st, 0, sizeof *st);
+      rc = read_stats(s, st, cs);
+      if (rc) return rc;
+      CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // includes the overlapped band copies
+      st->ms_total = st->ms_trace;
+      st->kernel_launches = launches;
+    }
+    return RTP_OK;
+  }
   if (!fused && (rgb || rgb8 || hit)) {
     launch_untile(f.fb.p, 0, f.local_of_tile.p, o->width, o->height, o->world, o->world > 1 ? o->rank : 0,
                   rgb ? f.out_rgb.p : nullptr, rgb8 ? f.out_rgb8.p : nullptr, hit ? f.out_hit.p : nullptr, cs);
@@ -701,7 +875,7 @@ int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max
   p.n_user_rays = (int)n;
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  rc = enqueue_frame(s, p, cs, &launches, false, (int)n);
+  rc = enqueue_frame(s, p, cs, &launches, false, (int)n, 1);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
   std::vector<float4> h((size_t)n);

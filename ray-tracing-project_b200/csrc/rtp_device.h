@@ -69,6 +69,16 @@ struct DeviceCamera {
 
 RTP_HD v3 xyz(float4 a) { return mk3(a.x, a.y, a.z); }
 
+// Pins a value to the point where it is used: the compiler may not hoist arithmetic that depends on it out
+// of the enclosing branch.  (ptxas otherwise evaluates the loop-invariant part of the reference BoundingBox
+// test - two 3x4 transforms, ~40 instructions - at every leaf visit, although only a hit candidate needs it.)
+#if defined(__CUDA_ARCH__)
+#define RTP_PIN(x) asm volatile("" : "+f"(x))
+#else
+#define RTP_PIN(x) ((void)0)
+#endif
+RTP_HD v3 pinned(v3 a) { RTP_PIN(a.x); RTP_PIN(a.y); RTP_PIN(a.z); return a; }
+
 // Traversal work counters: compiled in only for tests/hostsim (CPU, -DRTP_TRAV_STATS), where they
 // give nodes / leaves / triangle tests per ray for the roofline discussion in DESIGN.md.
 #if defined(RTP_TRAV_STATS) && !defined(__CUDA_ARCH__)
@@ -243,7 +253,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
       // tt <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
       // and t == +inf never beats the initial INFINITY.
       if (!ANY && !(tt < t.tbest || (t.sbest >= 0 && rank < t.rbest))) continue;
-      if ((ANY || t.careful) && !ref_box_pass(S, bo, t.d, f2i(T1.w))) continue;  // invisible to the reference
+      if ((ANY || t.careful) && !ref_box_pass(S, pinned(bo), pinned(t.d), f2i(T1.w))) continue;  // invisible to the reference
       t.tbest = ANY ? t.tbest : tt;
       t.rbest = rank;
       t.sbest = first + k;

@@ -211,7 +211,7 @@ __device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const 
           if (!tri_exact(S, first + j, o, d, tb, tt, T0, T1)) continue;
           const unsigned rank = (unsigned)f2i(T0.w);
           if (!ANY && !(tt < tb || (sb >= 0 && rank < rb))) continue;
-          if ((ANY || careful) && !ref_box_pass(S, bo, d, f2i(T1.w))) continue;
+          if ((ANY || careful) && !ref_box_pass(S, pinned(bo), pinned(d), f2i(T1.w))) continue;
           tb = ANY ? tb : tt;
           rb = rank;
           sb = first + j;
@@ -571,6 +571,8 @@ int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning 
 int g_budget = 12;      // RTP_BUDGET: steps before the last lanes of a warp count as stragglers (0: never park)
 int g_park_lanes = 4;   // RTP_PARK_LANES: ... when at most this many lanes are left
 int g_park_any = 0;     // RTP_PARK_ANY=1: park shadow rays too
+int g_budget_any = 12;  // RTP_BUDGET_ANY: step budget of shadow-ray launches (a step of an unoccluded ray is 32 nodes)
+int g_park_lanes_any = 4;
 int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
 
 // Refill policy: a warp refills its idle lanes from the global ray list when fewer than `refill`
@@ -588,17 +590,31 @@ int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters
     if ((e = std::getenv("RTP_BUDGET"))) g_budget = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_ANY"))) g_park_any = std::atoi(e);
+    g_budget_any = g_budget;
+    g_park_lanes_any = g_park_lanes;
+    if ((e = std::getenv("RTP_BUDGET_ANY"))) g_budget_any = std::atoi(e);
+    if ((e = std::getenv("RTP_PARK_LANES_ANY"))) g_park_lanes_any = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_SMALL"))) g_park_small = std::atoi(e);
   }
-  const int refill = g_refill >= 0 ? g_refill : (coherent ? 1 : 24);
+  static int refill_any = -2, refill_closest = -2;
+  if (refill_any == -2) {
+    const char *e = std::getenv("RTP_REFILL_ANY");
+    refill_any = e ? std::atoi(e) : -1;
+    e = std::getenv("RTP_REFILL_CLOSEST");
+    refill_closest = e ? std::atoi(e) : -1;
+  }
+  int refill = g_refill >= 0 ? g_refill : (coherent ? 1 : 24);
+  if (coherent && (Job::kAny ? refill_any : refill_closest) >= 0) refill = Job::kAny ? refill_any : refill_closest;
   ParkList pl;
   pl.slots = cfg.park_slots;
   pl.ctr = counters + kCtrPark + 2 * launch_slot;
   pl.cap = cfg.park_cap;
   const bool park = g_budget > 0 && cfg.park_slots && (!Job::kAny || g_park_any) && (cfg.scene_exceeds_l2 || g_park_small);
-  pl.budget = park ? g_budget : 0x3fffffff;
-  pl.lanes = g_park_lanes;
+  pl.budget = park ? (Job::kAny ? g_budget_any : g_budget) : 0x3fffffff;
+  pl.lanes = Job::kAny ? g_park_lanes_any : g_park_lanes;
   if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job, pl);
+  else if (refill <= 4) k_trace<Job, 4><<<blocks, threads, 0, st>>>(job, pl);
+  else if (refill <= 8) k_trace<Job, 8><<<blocks, threads, 0, st>>>(job, pl);
   else if (refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job, pl);
   else if (refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
   else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job, pl);
@@ -612,6 +628,10 @@ int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters
 void query_launch_cfg(int device, LaunchCfg &cfg) {
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  if (const char *e = std::getenv("RTP_TRACE_THREADS")) {  // tuning runs: 32, 64 or 128 threads per CTA
+    const int t = std::atoi(e);
+    if (t == 32 || t == 64 || t == 128) cfg.threads = t;
+  }
   int b0 = 1, b1 = 1;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_trace<FrameClosest, 24>, cfg.threads, 0);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny, 24>, cfg.threads, 0);

@@ -1,0 +1,60 @@
+"""Tile groups (rtp_set_tile_groups): a frame's tiles cut into bands that run as independent sub-frames on
+their own CUDA streams (csrc/rtp_api.cu: enqueue_frame).  Pixels never interact, so every output - float
+RGB, the quantised image copied band by band, primary face ids, ray counters - must be bit-identical for
+any number of groups, on one GPU and on a rank's share of a tile-sharded frame."""
+import numpy as np
+import pytest
+
+from conftest import bits_equal, load_case, load_golden_mesh
+
+pytestmark = pytest.mark.gpu
+
+
+def scene_for(rtp, case, w, h):
+    c = load_case(case)
+    m = load_golden_mesh(c["model"])
+    s = rtp.Scene(m.verts, m.normals, m.faces, m.face_mat, m.materials, m.shape)
+    s.set_lights(c["point_lights"], c["dir_lights"])
+    s.set_camera(w, h, c["view"])
+    return s, c
+
+
+@pytest.mark.parametrize("case,w,h,depth", [("dodge_c2", 640, 360, 4), ("testding_2l", 200, 130, 3), ("glas_nan", 96, 96, 2)])
+def test_image_does_not_depend_on_the_group_count(rtp, case, w, h, depth):
+    s, c = scene_for(rtp, case, w, h)
+    ref = None
+    for g in (1, 2, 3, 5, 8, 0):
+        s.set_tile_groups(g)
+        a = s.render(w, h, max_depth=depth, want=("rgb", "rgb8", "hit"))      # un-tile path
+        b = s.render(w, h, max_depth=depth, want=("rgb8", "hit"))             # fused resolve + band copies
+        rows = (h + 31) // 32
+        assert s.tile_groups() == (min(g, rows) if g else max(1, min(3, rows * ((w + 31) // 32) // 64)))
+        assert np.array_equal(a["rgb8"], b["rgb8"]) and np.array_equal(a["hit"], b["hit"])
+        cur = (a["rgb"], a["rgb8"], a["hit"], [a["stats"][k] for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits")])
+        if ref is None:
+            ref = cur
+            continue
+        assert bits_equal(cur[0], ref[0]).all(), f"groups={g}: float RGB differs"
+        assert np.array_equal(cur[1], ref[1]) and np.array_equal(cur[2], ref[2])
+        assert cur[3] == ref[3]
+    s.close()
+
+
+def test_groups_on_a_rank_share(rtp):
+    """world = 3: a rank's interleaved tiles are split by count (not by rows); same tile buffer either way."""
+    import torch
+    w, h = 500, 300
+    s, c = scene_for(rtp, "dodge_c2", w, h)
+    for rank in range(3):
+        nbytes = rtp.tile_buffer_bytes(w, h, rank, 3)
+        bufs = []
+        for g in (1, 4):
+            s.set_tile_groups(g)
+            t = torch.zeros(nbytes // 4, dtype=torch.float32, device="cuda")
+            s.render_tiles_device(w, h, t.data_ptr(), max_depth=3, rank=rank, world=3,
+                                  stream=torch.cuda.current_stream().cuda_stream)
+            torch.cuda.synchronize()
+            bufs.append(t.cpu().numpy().view(np.uint32))
+        n_own = len(rtp.tile_table(w, h, rank, 3)[0]) * 1024 * 4
+        assert np.array_equal(bufs[0][:n_own], bufs[1][:n_own])
+    s.close()
