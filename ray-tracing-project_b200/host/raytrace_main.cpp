@@ -5,9 +5,12 @@
 //   raytrace [--model DIR/FILE.obj] [--size W H] [--depth MAX_DEPTH] [--fovy DEG]
 //            [--view m0..m11] [--light x y z r g b]... [--dirlight x y z r g b]... [--nolights]
 //            [--soft x y z r g b RADIUS N] [--out result.ppm] [--device N] [--dump-scene PREFIX]
+//            [--serial-obj]                  with --dump-scene: the line-by-line OBJ loader instead of the parallel one
 //            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
 //            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
 #include <array>
+#include <chrono>
+#include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -33,10 +36,15 @@ int usage() {
 }
 
 // Loads and flattens exactly as Flyscene::initialize does, without touching CUDA.
-int dump_scene(const std::string &model, const std::string &prefix, int min_faces) {
+int dump_scene(const std::string &model, const std::string &prefix, int min_faces, bool serial_obj, bool load_only) {
   Tucano::Mesh mesh;
   std::vector<Tucano::Material::Mtl> materials;
-  Tucano::MeshImporter::loadObjFile(mesh, materials, model);
+  const auto t0 = std::chrono::steady_clock::now();
+  if (serial_obj) Tucano::MeshImporter::loadObjFileSerial(mesh, materials, model);
+  else Tucano::MeshImporter::loadObjFile(mesh, materials, model);
+  fprintf(stderr, "obj load (%s): %.3f s\n", serial_obj ? "serial" : "parallel",
+          std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
+  if (load_only) min_faces = INT_MAX;  // --dump-scene-noboxes: one box, no splitter (timing / large synthetic meshes)
   mesh.normalizeModelMatrix();
   const int V = mesh.getNumberOfVertices(), F = mesh.getNumberOfFaces();
   if (F == 0) return 1;
@@ -131,7 +139,7 @@ int main(int argc, char **argv) {
   std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out;
   int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
   float fovy = 60.f;
-  bool has_view = false, nolights = false;
+  bool has_view = false, nolights = false, serial_obj = false, load_only = false;
   float view[12];
   std::vector<std::array<float, 6>> lights, dirlights;
   std::vector<std::array<float, 8>> soft;
@@ -145,6 +153,8 @@ int main(int argc, char **argv) {
     else if (a == "--device") { need(i, 1); device = atoi(argv[++i]); }
     else if (a == "--out") { need(i, 1); out = argv[++i]; }
     else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
+    else if (a == "--dump-scene-noboxes") { need(i, 1); dump_prefix = argv[++i]; load_only = true; }
+    else if (a == "--serial-obj") serial_obj = true;
     else if (a == "--dump-rays") { need(i, 1); rays_prefix = argv[++i]; }
     else if (a == "--ppm-from-f32") { need(i, 2); f32_in = argv[++i]; f32_out = argv[++i]; }
     else if (a == "--nolights") nolights = true;
@@ -161,7 +171,7 @@ int main(int argc, char **argv) {
       soft.push_back(l);
     } else return usage();
   }
-  if (!dump_prefix.empty()) return dump_scene(model, dump_prefix, 300);
+  if (!dump_prefix.empty()) return dump_scene(model, dump_prefix, 300, serial_obj, load_only);
   if (!rays_prefix.empty()) return dump_rays(rays_prefix, W, H, fovy, has_view ? view : nullptr);
   if (!f32_in.empty()) return ppm_from_f32(f32_in, f32_out, W, H);
 

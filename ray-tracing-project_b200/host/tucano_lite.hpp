@@ -18,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include "../csrc/parallel_for.h"
 #include "eigen_lite.hpp"
 
 typedef unsigned int GLuint;
@@ -124,24 +125,35 @@ class Mesh : public Model {
     for (unsigned int i = 0; i < numberOfVertices; i++) radius = std::max(radius, (vert[i].head3() - centroid).norm());
   }
 
-  // mesh.hpp:448-482: one Face per index triple; normal from the NORMALISED object-space edges
+  // mesh.hpp:448-482: one Face per index triple; normal from the NORMALISED object-space edges.
+  // Faces are independent of each other, so the index groups are filled by all host threads (same bits).
   void createFaces() {
     if (vertices.empty() || indices_vertices.empty()) return;
+    std::vector<size_t> first(indices_vertices.size() + 1, faces.size());
+    for (size_t id = 0; id < indices_vertices.size(); ++id)
+      first[id + 1] = first[id] + indices_vertices[id].size() / 3;  // a trailing partial triple is dropped (UB in the original)
+    faces.resize(first.back());
     for (size_t id = 0; id < indices_vertices.size(); ++id) {
       const std::vector<GLuint> &ix = indices_vertices[id];
-      for (size_t i = 0; i + 2 < ix.size(); i = i + 3) {  // a trailing partial triple is dropped (UB in the original)
-        Face f;
-        f.vertex_ids.push_back(ix[i]);
-        f.vertex_ids.push_back(ix[i + 1]);
-        f.vertex_ids.push_back(ix[i + 2]);
-        if (!material_ids.empty()) f.material_id = material_ids[id];
-        const rtp::v3 a = vertices[ix[i]].head3().r(), b = vertices[ix[i + 1]].head3().r(), c = vertices[ix[i + 2]].head3().r();
-        // .head(3) differences are dynamic-size expressions: sequential squaredNorm reduction
-        const rtp::v3 v1 = rtp::vnormalized_dyn(rtp::vsub(c, a));
-        const rtp::v3 v0 = rtp::vnormalized_dyn(rtp::vsub(b, a));
-        f.normal = Eigen::Vector3f(rtp::vnormalized(rtp::vcross(v0, v1)));
-        faces.push_back(f);
-      }
+      const int mat = material_ids.empty() ? -1 : material_ids[id];
+      const bool has_mat = !material_ids.empty();
+      Face *out = faces.data() + first[id];
+      rtp::parallel_for(ix.size() / 3, 0, 8192, [&](size_t b, size_t e, int) {
+        for (size_t k = b; k < e; ++k) {
+          const size_t i = 3 * k;
+          Face &f = out[k];
+          f.vertex_ids.reserve(3);
+          f.vertex_ids.push_back(ix[i]);
+          f.vertex_ids.push_back(ix[i + 1]);
+          f.vertex_ids.push_back(ix[i + 2]);
+          if (has_mat) f.material_id = mat;
+          const rtp::v3 a = vertices[ix[i]].head3().r(), b3 = vertices[ix[i + 1]].head3().r(), c = vertices[ix[i + 2]].head3().r();
+          // .head(3) differences are dynamic-size expressions: sequential squaredNorm reduction
+          const rtp::v3 v1 = rtp::vnormalized_dyn(rtp::vsub(c, a));
+          const rtp::v3 v0 = rtp::vnormalized_dyn(rtp::vsub(b3, a));
+          f.normal = Eigen::Vector3f(rtp::vnormalized(rtp::vcross(v0, v1)));
+        }
+      });
     }
   }
 };

@@ -149,3 +149,52 @@ def test_flyscene_soft_light_and_single_ray_api(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     w, h, got = ppm_values(out)
     assert (w, h) == (40, 40) and got.min() >= 0 and got.max() <= 255
+
+
+DUMPS = ["verts.f32", "normals.f32", "faces.i32", "fmat.i32", "materials.f32", "shape.f32", "fnormal.f32", "boxes.f32",
+         "box_off.i32", "box_faces.i32"]
+
+NASTY_OBJ = (
+    "# numbers and face tokens the two loaders must read alike\r\n"
+    "mtllib quirks.mtl\r\n"
+    "v +1.5 -2e-1 .5\n"
+    "v 1 2\n"                       # third component missing: stays 0
+    "v 1e 2 3\n"                    # malformed exponent: the stream fails, everything after it stays 0
+    "v   0.25\t-0.125   1E+1 0.9 0.8 0.7\n"   # vertex colours after xyz are ignored
+    "v 1e-50 1e39 -0\n"             # underflow / overflow of float
+    "v 3 1 4\nv 1 5 9\nv 2 6 5\nv 3 5 8\n"
+    "vn 0 0 1\n"                    # #vn != #v: normals are recomputed
+    "usemtl nosuchmaterial\n"
+    "f 1/2/3 2//7 3\n"
+    "f 4 x 5/1 /3 +6 7 8 99999999999\n"   # std::stoi throws on non-numbers and on overflow: those tokens are skipped
+    "usemtl red\n"
+    "usemtl blue\n"                 # empty group: no new index list
+    "f 6/1 7/2 8/3 9\n"
+    "f 2 3 4"                        # no newline at the end of the file
+)
+
+
+@pytest.mark.parametrize("name", ["quirks", "nasty"] + SHIPPED)
+def test_parallel_obj_ingest_equals_the_line_by_line_loader(name, tmp_path):
+    """the mapped, multi-threaded OBJ parser fills the Mesh with the same bits as the
+    reference-shaped iostream loader, for any number of ranges the file is cut into."""
+    need_cli()
+    if name == "nasty":
+        path = str(tmp_path / "nasty.obj")
+        open(path, "w", newline="").write(NASTY_OBJ)
+        open(str(tmp_path / "quirks.mtl"), "w").write(open(os.path.join(GOLDEN, "quirks.mtl")).read())
+    else:
+        path = model_path(name)
+    flag = "--dump-scene"
+    ref = str(tmp_path / "serial")
+    r = subprocess.run([CLI, "--model", path, flag, ref, "--serial-obj"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for threads, chunk in ((1, 1 << 16), (3, 64), (8, 17), (8, 1 << 16)):
+        pre = str(tmp_path / f"par{threads}_{chunk}")
+        env = dict(os.environ, RTP_OBJ_THREADS=str(threads), RTP_OBJ_MIN_CHUNK=str(chunk))
+        r2 = subprocess.run([CLI, "--model", path, flag, pre], capture_output=True, text=True, env=env)
+        assert r2.returncode == 0, r2.stderr
+        assert [l for l in r2.stdout.splitlines() if "number" in l] == [l for l in r.stdout.splitlines() if "number" in l]
+        for suffix in DUMPS:
+            a, b = np.fromfile(f"{ref}.{suffix}", np.uint32), np.fromfile(f"{pre}.{suffix}", np.uint32)
+            assert np.array_equal(a, b), f"{name}: {suffix} differs with {threads} threads / {chunk}-byte ranges"
