@@ -133,6 +133,16 @@ int rtp_get_tile_groups(const rtp_scene *s); /* bands the most recently enqueued
 int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8, int32_t *hit,
                rtp_stats *st);
 
+/* Multi-frame renders (a camera path): rtp_render_async returns as soon as the frame is enqueued, rtp_render_wait
+ * blocks until the OLDEST outstanding frame has landed in its host buffers and returns its statistics.  Two
+ * frames may be outstanding: the device image planes are double-buffered and the band copies run on their own
+ * streams, so frame k+1 is traced while frame k is still on its way to the host.  rgb8 / hit as in rtp_render
+ * (at least one; page-locked memory, e.g. cudaHostAlloc, for a real overlap); camera and lights are the ones set
+ * when the call is made.  One GPU per scene (world must be 1).  No counterpart in the reference, whose
+ * raytraceScene renders one frame per key press (main.cpp:68-69). */
+int rtp_render_async(rtp_scene *s, const rtp_render_opts *o, uint8_t *rgb8, int32_t *hit);
+int rtp_render_wait(rtp_scene *s, rtp_stats *st /* may be NULL */);
+
 /* Device-resident variant used by multi-GPU drivers: renders this rank's interleaved screen
  * tiles into a compact tile-major buffer of float4 (r, g, b, bit-cast primary face id) in
  * device memory.  d_tiles: rtp_tile_buffer_bytes() bytes of device memory owned by the caller

@@ -61,7 +61,7 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
+           "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_render_async", "rtp_render_wait", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
            "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free"]
 
 _lib = None
@@ -88,6 +88,8 @@ def lib():
         L.rtp_set_camera.argtypes = [C.c_void_p, C.POINTER(RtpCamera)]
         L.rtp_set_tile_groups.argtypes = [C.c_void_p, C.c_int]
         L.rtp_get_tile_groups.argtypes = [C.c_void_p]
+        L.rtp_render_async.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p]
+        L.rtp_render_wait.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
         L.rtp_render.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.POINTER(RtpStats)]
         L.rtp_render_tiles_device.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p,
@@ -259,6 +261,17 @@ class Scene:
         self._check(self._L.rtp_render(self._h, C.byref(o), ptr("rgb"), ptr("rgb8"), ptr("hit"), C.byref(st)))
         out["stats"] = st.as_dict()
         return out
+
+    def render_async(self, w, h, rgb8_ptr=None, hit_ptr=None, max_depth=2, background=BACKGROUND):
+        """rtp_render_async: enqueue one frame into (page-locked) host buffers given by address; at most two outstanding."""
+        o = make_opts(w, h, max_depth, background, 0, 1, 0)
+        self._check(self._L.rtp_render_async(self._h, C.byref(o), rgb8_ptr, hit_ptr))
+
+    def render_wait(self):
+        """rtp_render_wait: blocks until the oldest outstanding frame is in its host buffers; returns its stats."""
+        st = RtpStats()
+        self._check(self._L.rtp_render_wait(self._h, C.byref(st)))
+        return st.as_dict()
 
     def render_tiles_device(self, w, h, d_tiles_ptr, max_depth=2, background=BACKGROUND, rank=0, world=1,
                             stream=None, want_stats=False, flags=0):

@@ -84,6 +84,7 @@ struct rtp_scene {
   DevBuf<int> counters;
   DevBuf<int> park;  // parked-ray list of the trace kernels
   DeviceScene dS;
+  std::vector<float4> lights_host;  // what s->lights holds
   DeviceCamera cam;
   bool have_camera = false, have_lights = false;
   LaunchCfg cfg;
@@ -92,6 +93,20 @@ struct rtp_scene {
   // tile groups of a frame run on their own streams (enqueue_frame): group 0 on the caller's stream
   cudaStream_t gstream[kMaxGroups] = {};
   cudaEvent_t gfork = nullptr, gjoin[kMaxGroups] = {};
+  // rtp_render_async: two frames may be outstanding; image planes, counters snapshot and events per slot,
+  // band copies on their own streams so that the next frame's kernels do not queue behind them
+  struct AsyncSlot {
+    DevBuf<unsigned char> rgb8;
+    DevBuf<int> hit;
+    int *counters_host = nullptr;  // pinned, kCtrInts * kMaxGroups
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, copied[kMaxGroups] = {};
+    int groups = 1, launches = 0, primary = 0, depth = 0, lights = 0;
+    bool busy = false;
+  } aslot[2];
+  cudaStream_t cstream[kMaxGroups] = {};
+  cudaEvent_t resolved[kMaxGroups] = {};
+  unsigned async_head = 0, async_tail = 0;  // frames enqueued / waited for
+  bool in_async_call = false;
   int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
   int last_groups = 1;  // groups of the most recently enqueued frame (their counters are summed)
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
@@ -254,6 +269,17 @@ int rtp_scene_destroy(rtp_scene *s) {
     if (s->gjoin[i]) cudaEventDestroy(s->gjoin[i]);
   }
   if (s->gfork) cudaEventDestroy(s->gfork);
+  for (int i = 0; i < kMaxGroups; ++i) {
+    if (s->cstream[i]) { cudaStreamSynchronize(s->cstream[i]); cudaStreamDestroy(s->cstream[i]); }
+    if (s->resolved[i]) cudaEventDestroy(s->resolved[i]);
+  }
+  for (auto &a : s->aslot) {
+    if (a.counters_host) cudaFreeHost(a.counters_host);
+    if (a.ev0) cudaEventDestroy(a.ev0);
+    if (a.ev1) cudaEventDestroy(a.ev1);
+    for (auto &e : a.copied)
+      if (e) cudaEventDestroy(e);
+  }
   delete s;  // DevBuf destructors free device memory while the device is current
   return RTP_OK;
 }
@@ -265,8 +291,16 @@ int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
   DeviceGuard g(s->device);
   std::vector<float4> packed;
   pack_lights(*l, packed);
-  CK(s->lights.upload(packed, s->stream));
-  CK(cudaStreamSynchronize(s->stream));
+  // unchanged light set (a render loop sets it before every frame): nothing to upload.  Otherwise the copy is
+  // stream-ordered behind the previous frame (all its tile groups are joined into s->stream) and does not block
+  // the host: frames of rtp_render_async stay in flight.  A re-allocation (more lights than ever before) waits.
+  const bool same = s->have_lights && packed.size() == s->lights_host.size() &&
+                    (packed.empty() || std::memcmp(packed.data(), s->lights_host.data(), packed.size() * sizeof(float4)) == 0);
+  if (!same) {
+    if (packed.size() > s->lights.n && s->has_last) CK(cudaStreamSynchronize(s->last_stream));
+    s->lights_host = packed;  // the source of the asynchronous copy stays alive in the scene
+    CK(s->lights.upload(s->lights_host, s->has_last ? s->last_stream : s->stream));
+  }
   s->dS.lights = s->lights.p;
   s->dS.n_lights = l->n_point + l->n_dir;
   s->have_lights = true;
@@ -526,34 +560,41 @@ int check_render_args(rtp_scene *s, const rtp_render_opts *o) {
     return fail(RTP_ERR_INVALID, "render: bad image size");
   if (o->max_depth < 1 || o->max_depth > kMaxDepth) return fail(RTP_ERR_INVALID, "render: max_depth must be in [1, 8]");
   if (o->world < 1 || o->rank < 0 || o->rank >= o->world) return fail(RTP_ERR_INVALID, "render: bad rank/world");
+  if (s->async_head != s->async_tail && !s->in_async_call)
+    return fail(RTP_ERR_STATE, "render: frames of rtp_render_async are outstanding (call rtp_render_wait first)");
   if (!s->have_camera) return fail(RTP_ERR_STATE, "render: rtp_set_camera has not been called");
   if (!s->have_lights) return fail(RTP_ERR_STATE, "render: rtp_set_lights has not been called");
   return RTP_OK;
 }
 
+// ray counting rule of SURVEY.md 8(d): 1 primary per pixel; per hit one shadow ray per light and, below the
+// depth limit, one reflection ray.  hg: the counter blocks of the frame's G tile groups.
+void stats_from_counters(const rtp_scene *s, const int *hg, int G, int primary, int depth, int lights, rtp_stats *st) {
+  int h[kCtrInts] = {};
+  for (int g = 0; g < G; ++g)
+    for (int i = 0; i < kCtrInts; ++i) h[i] += hg[g * kCtrInts + i];
+  st->rays_primary = primary;
+  for (int d = 0; d < depth; ++d) {
+    st->hits += h[kCtrHits + d];
+    if (d > 0) st->rays_reflection += h[kCtrPaths + d];
+  }
+  st->rays_shadow = st->hits * lights;
+  st->n_bvh_nodes = s->host.n_nodes;
+  st->n_triangles = s->host.n_tris;
+}
+
 int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
-  int hg[kCtrInts * kMaxGroups], h[kCtrInts] = {};
+  int hg[kCtrInts * kMaxGroups];
   const int G = std::min(std::max(s->last_groups, 1), kMaxGroups);
   CK(cudaMemcpyAsync(hg, s->counters.p, (size_t)kCtrInts * G * sizeof(int), cudaMemcpyDeviceToHost, stream));
   CK(cudaStreamSynchronize(stream));
-  for (int g = 0; g < G; ++g)
-    for (int i = 0; i < kCtrInts; ++i) h[i] += hg[g * kCtrInts + i];
   for (int i = 0; i + 1 < s->kev_used; ++i) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, s->kev[i], s->kev[i + 1]));
     const int kind = s->kev_kind[(size_t)i];
     (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : st->ms_shade) += ms;
   }
-  // ray counting rule of SURVEY.md 8(d): 1 primary per pixel; per hit one shadow ray per light and,
-  // below the depth limit, one reflection ray
-  st->rays_primary = s->last_primary;
-  for (int d = 0; d < s->last_depth; ++d) {
-    st->hits += h[kCtrHits + d];
-    if (d > 0) st->rays_reflection += h[kCtrPaths + d];
-  }
-  st->rays_shadow = st->hits * s->last_lights;
-  st->n_bvh_nodes = s->host.n_nodes;
-  st->n_triangles = s->host.n_tris;
+  stats_from_counters(s, hg, G, s->last_primary, s->last_depth, s->last_lights, st);
   return RTP_OK;
 }
 
@@ -790,6 +831,99 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
     CK(cudaEventElapsedTime(&st->ms_total, s->ev[0], s->ev[2]));
     st->kernel_launches = launches;
   }
+  return RTP_OK;
+}
+
+int rtp_render_async(rtp_scene *s, const rtp_render_opts *o, uint8_t *rgb8, int32_t *hit) {
+  if (s) s->in_async_call = true;
+  int rc = check_render_args(s, o);
+  if (s) s->in_async_call = false;
+  if (rc) return rc;
+  if (!rgb8 && !hit) return fail(RTP_ERR_INVALID, "rtp_render_async: no output plane");
+  if (o->world != 1) return fail(RTP_ERR_INVALID, "rtp_render_async: one GPU per scene (world must be 1)");
+  if (o->flags & RTP_RENDER_PROFILE) return fail(RTP_ERR_INVALID, "rtp_render_async: RTP_RENDER_PROFILE needs the synchronous call");
+  if (s->async_head - s->async_tail >= 2) return fail(RTP_ERR_STATE, "rtp_render_async: two frames are already outstanding");
+  DeviceGuard g(s->device);
+  cudaStream_t cs = s->stream;
+  rtp_scene::AsyncSlot &a = s->aslot[s->async_head & 1];
+  if (!a.counters_host) {  // first use of the slot
+    CK(cudaHostAlloc((void **)&a.counters_host, sizeof(int) * kCtrInts * kMaxGroups, cudaHostAllocDefault));
+    CK(cudaEventCreate(&a.ev0));
+    CK(cudaEventCreate(&a.ev1));
+    for (auto &e : a.copied) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  }
+  for (int i = 0; i < kMaxGroups; ++i)
+    if (!s->cstream[i]) {
+      CK(cudaStreamCreateWithFlags(&s->cstream[i], cudaStreamNonBlocking));
+      CK(cudaEventCreateWithFlags(&s->resolved[i], cudaEventDisableTiming));
+    }
+  Frame &f = s->frame;
+  const int n_px = own_tile_count(o->width, o->height, 0, 1) * kTilePixels;
+  rc = ensure_frame(s, f, o->width, o->height, 0, 1, std::max(o->max_depth, 1), n_px, true);
+  if (rc) return rc;
+  const size_t npix = (size_t)o->width * o->height;
+  if (rgb8) CK(a.rgb8.ensure(npix * 3));
+  if (hit) CK(a.hit.ensure(npix));
+  FrameParams p;
+  fill_params(s, f, *o, nullptr, p);
+  p.img_rgb8 = rgb8 ? a.rgb8.p : nullptr;
+  p.img_hit = hit ? a.hit.p : nullptr;
+  const int tiles_x = f.tiles_x, width = o->width, height = o->height;
+  unsigned char *d_rgb8 = a.rgb8.p;
+  int *d_hit = a.hit.p;
+  int n_groups = 0;
+  // a band's copy runs on the copy stream of its group, behind the band's resolve kernel only: the group's own
+  // stream is free for the next frame at once
+  auto copy_band = [&](int gi, int t0, int t1, cudaStream_t gs) -> cudaError_t {
+    n_groups = std::max(n_groups, gi + 1);
+    cudaError_t e = cudaEventRecord(s->resolved[gi], gs);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(s->cstream[gi], s->resolved[gi], 0);
+    const size_t y0 = (size_t)(t0 / tiles_x) * kTileDim;
+    const size_t y1 = std::min<size_t>((size_t)height, (size_t)((t1 + tiles_x - 1) / tiles_x) * kTileDim);
+    if (e == cudaSuccess && rgb8 && y1 > y0)
+      e = cudaMemcpyAsync(rgb8 + y0 * width * 3, d_rgb8 + y0 * width * 3, (y1 - y0) * width * 3, cudaMemcpyDeviceToHost, s->cstream[gi]);
+    if (e == cudaSuccess && hit && y1 > y0)
+      e = cudaMemcpyAsync(hit + y0 * width, d_hit + y0 * width, (y1 - y0) * width * sizeof(int), cudaMemcpyDeviceToHost, s->cstream[gi]);
+    if (e == cudaSuccess) e = cudaEventRecord(a.copied[gi], s->cstream[gi]);
+    return e;
+  };
+  int launches = 0;
+  CK(cudaEventRecord(a.ev0, cs));
+  rc = enqueue_frame(s, p, cs, &launches, false, f.n_valid, 1, copy_band);
+  if (rc) return rc;
+  CK(cudaEventRecord(a.ev1, cs));
+  // the frame's counters, before the next frame zeroes them (stream order)
+  CK(cudaMemcpyAsync(a.counters_host, s->counters.p, sizeof(int) * kCtrInts * (size_t)s->last_groups, cudaMemcpyDeviceToHost, cs));
+  a.groups = n_groups;
+  a.launches = launches;
+  a.primary = f.n_valid;
+  a.depth = o->max_depth;
+  a.lights = s->dS.n_lights;
+  a.busy = true;
+  ++s->async_head;
+  return RTP_OK;
+}
+
+int rtp_render_wait(rtp_scene *s, rtp_stats *st) {
+  if (!s) return fail(RTP_ERR_INVALID, "rtp_render_wait: null scene");
+  if (s->async_head == s->async_tail) return fail(RTP_ERR_STATE, "rtp_render_wait: no frame outstanding");
+  DeviceGuard g(s->device);
+  rtp_scene::AsyncSlot &a = s->aslot[s->async_tail & 1];
+  for (int gi = 0; gi < a.groups; ++gi) CK(cudaEventSynchronize(a.copied[gi]));
+  // the counters copy is the last operation of the frame on the scene's stream; ev1 precedes it
+  CK(cudaEventSynchronize(a.ev1));
+  if (st) {
+    std::memset(st, 0, sizeof *st);
+    // wait for the counters snapshot itself: it was enqueued right after ev1 on the same stream
+    if (s->async_head - s->async_tail == 1) CK(cudaStreamSynchronize(s->stream));
+    else CK(cudaEventSynchronize(s->aslot[(s->async_tail + 1) & 1].ev0));  // recorded after that copy
+    stats_from_counters(s, a.counters_host, std::max(a.groups, 1), a.primary, a.depth, a.lights, st);
+    CK(cudaEventElapsedTime(&st->ms_trace, a.ev0, a.ev1));
+    st->ms_total = st->ms_trace;
+    st->kernel_launches = a.launches;
+  }
+  a.busy = false;
+  ++s->async_tail;
   return RTP_OK;
 }
 

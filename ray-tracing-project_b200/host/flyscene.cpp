@@ -150,7 +150,8 @@ void Flyscene::raytraceScene(int width, int height) {  // flyscene.cpp:250-297
   o.rank = 0; o.world = 1; o.flags = RTP_RENDER_DEFAULT;
   std::vector<float> rgb(3 * (size_t)W * H);
   primary_hits.assign((size_t)W * H, -1);
-  if (rtp_render(scene, &o, rgb.data(), nullptr, primary_hits.data(), &last_stats) != RTP_OK) {
+  image8.assign(3 * (size_t)W * H, 0);
+  if (rtp_render(scene, &o, rgb.data(), image8.data(), primary_hits.data(), &last_stats) != RTP_OK) {
     fail("rtp_render");
     return;
   }
@@ -162,6 +163,7 @@ void Flyscene::raytraceScene(int width, int height) {  // flyscene.cpp:250-297
   }
   PIXEL_COUNT = H;
   if (!OUTPUT_NAME.empty()) Tucano::ImageImporter::writePPMImage(OUTPUT_NAME, pixel_data);  // :292
+  if (!OUTPUT_BINARY_NAME.empty()) Tucano::ImageImporter::writePPMImageBinary(OUTPUT_BINARY_NAME, image8.data(), W, H);
   const time_t end_time = time(NULL);
   std::cout << "ray tracing done! " << std::endl;
   std::cout << "Runtime: " << (end_time - start_time) << " seconds (device " << last_stats.ms_total << " ms, "
@@ -257,6 +259,30 @@ void Flyscene::sphericalLight(std::pair<Eigen::Vector3f, Eigen::Vector3f> light,
     float y = (-radius + (rand() / (RAND_MAX / (radius * 2))));
     float z = (-radius + (rand() / (RAND_MAX / (radius * 2))));
     lights.push_back(std::pair<Eigen::Vector3f, Eigen::Vector3f>(Eigen::Vector3f(lightLoc.x() + x, lightLoc.y() + y, lightLoc.z() + z),
+                                                                 light.second / (float)(nLightpoints + 1)));
+  }
+}
+
+namespace {
+// SplitMix64 finaliser as a counter-based generator: value k of stream `seed` is a pure function of (seed, k).
+inline unsigned long long mix64(unsigned long long x) {
+  x += 0x9e3779b97f4a7c15ull;
+  x = (x ^ (x >> 30)) * 0xbf58476d1ce4e5b9ull;
+  x = (x ^ (x >> 27)) * 0x94d049bb133111ebull;
+  return x ^ (x >> 31);
+}
+}  // namespace
+
+void Flyscene::sphericalLightSeeded(std::pair<Eigen::Vector3f, Eigen::Vector3f> light, float radius, int nLightpoints, unsigned long long seed) {
+  Eigen::Vector3f lightLoc = light.first;
+  for (int i = 0; i < nLightpoints; i++) {
+    float j[3];
+    for (int c = 0; c < 3; ++c) {
+      // same cube [-radius, radius)^3 as sphericalLight; 24 random bits -> [0, 1)
+      const unsigned long long r = mix64(seed * 0x100000001b3ull + (unsigned long long)(3 * i + c));
+      j[c] = -radius + (radius * 2) * ((float)(r >> 40) * (1.0f / 16777216.0f));
+    }
+    lights.push_back(std::pair<Eigen::Vector3f, Eigen::Vector3f>(Eigen::Vector3f(lightLoc.x() + j[0], lightLoc.y() + j[1], lightLoc.z() + j[2]),
                                                                  light.second / (float)(nLightpoints + 1)));
   }
 }

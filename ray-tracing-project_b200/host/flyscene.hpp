@@ -74,9 +74,15 @@ class Flyscene {
   // n extra point lights jittered in a cube of half-edge `radius` with libc rand(), each carrying
   // rgb / (n + 1) (flyscene.cpp:529-538).
   void sphericalLight(std::pair<Eigen::Vector3f, Eigen::Vector3f> lightLoc, float radius, int nLightpoints);
+  // Same light set from a counter-based generator instead of libc rand() (a documented
+  // deviation: the reference's soft shadows differ from run to run and from libc to libc; these do not).
+  // Point i of the set depends on (seed, i) only.  Every point becomes one more shadow ray per hit; the
+  // device traces the shadow rays of ALL lights of a bounce level in one any-hit launch.
+  void sphericalLightSeeded(std::pair<Eigen::Vector3f, Eigen::Vector3f> lightLoc, float radius, int nLightpoints, unsigned long long seed);
 
   // ---- results of the last raytraceScene (the reference keeps them local and only writes the file)
   const std::vector<std::vector<Eigen::Vector3f>> &getPixelData() const { return pixel_data; }
+  const std::vector<unsigned char> &getImage8() const { return image8; }  // W*H*3, the values result.ppm holds (device-quantised)
   const std::vector<int> &getPrimaryHits() const { return primary_hits; }  // W*H face ids, -1 = background
   const rtp_stats &getLastStats() const { return last_stats; }
   rtp_scene *getDeviceScene() { return scene; }
@@ -106,6 +112,7 @@ class Flyscene {
   std::string error;
   std::vector<std::vector<Eigen::Vector3f>> pixel_data;
   std::vector<int> primary_hits;
+  std::vector<unsigned char> image8;
   rtp_stats last_stats = rtp_stats();
 
   void generateBoundingBoxes();
@@ -117,6 +124,7 @@ class Flyscene {
   std::string OBJECT_NAME = "dodgeColorTest.obj";
   std::string MODEL_DIR = "resources/models/";  // cwd-relative, as flyscene.cpp:18
   std::string OUTPUT_NAME = "result.ppm";       // flyscene.cpp:292; empty: no file
+  std::string OUTPUT_BINARY_NAME = "";          // non-empty: also write a binary P6 PPM of the device-quantised image
   int DEVICE = -1;                               // CUDA ordinal (-1: current device)
 
   static const bool RENDER_BOUNDINGBOXES = false;

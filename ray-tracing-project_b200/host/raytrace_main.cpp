@@ -4,7 +4,9 @@
 //
 //   raytrace [--model DIR/FILE.obj] [--size W H] [--depth MAX_DEPTH] [--fovy DEG]
 //            [--view m0..m11] [--light x y z r g b]... [--dirlight x y z r g b]... [--nolights]
-//            [--soft x y z r g b RADIUS N] [--out result.ppm] [--device N] [--dump-scene PREFIX]
+//            [--soft x y z r g b RADIUS N] [--seed S]   soft light: N jittered point lights (libc rand, or with --seed
+//                                            the counter-based generator of Flyscene::sphericalLightSeeded)
+//            [--out result.ppm] [--out-p6 result_p6.ppm] [--device N] [--dump-scene PREFIX] [--dump-lights PREFIX]
 //            [--serial-obj]                  with --dump-scene: the line-by-line OBJ loader instead of the parallel one
 //            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
 //            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
@@ -136,7 +138,9 @@ int ppm_from_f32(const std::string &in, const std::string &out, int W, int H) {
 }  // namespace
 
 int main(int argc, char **argv) {
-  std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out;
+  std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out, out_p6, lights_prefix;
+  unsigned long long seed = 0;
+  bool seeded = false;
   int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
   float fovy = 60.f;
   bool has_view = false, nolights = false, serial_obj = false, load_only = false;
@@ -152,6 +156,9 @@ int main(int argc, char **argv) {
     else if (a == "--fovy") { need(i, 1); fovy = (float)atof(argv[++i]); }
     else if (a == "--device") { need(i, 1); device = atoi(argv[++i]); }
     else if (a == "--out") { need(i, 1); out = argv[++i]; }
+    else if (a == "--out-p6") { need(i, 1); out_p6 = argv[++i]; }
+    else if (a == "--seed") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); seeded = true; }
+    else if (a == "--dump-lights") { need(i, 1); lights_prefix = argv[++i]; }
     else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
     else if (a == "--dump-scene-noboxes") { need(i, 1); dump_prefix = argv[++i]; load_only = true; }
     else if (a == "--serial-obj") serial_obj = true;
@@ -196,10 +203,17 @@ int main(int argc, char **argv) {
     flyscene->dirLights.push_back(std::make_tuple(Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5]), Eigen::Quaternion<float>()));
   for (auto &l : soft) {  // what addLight's "s" branch does (flyscene.cpp:213-236)
     std::pair<Eigen::Vector3f, Eigen::Vector3f> light(Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5]));
-    flyscene->sphericalLight(light, l[6], (int)l[7]);
+    if (seeded) flyscene->sphericalLightSeeded(light, l[6], (int)l[7], seed);
+    else flyscene->sphericalLight(light, l[6], (int)l[7]);
     light.second /= (float)((int)l[7] + 1);
     flyscene->lights.push_back(light);
   }
+  if (!lights_prefix.empty()) {  // the light set the frame is rendered with (tests: seeded soft lights are reproducible)
+    std::vector<float> lf;
+    for (auto &l : flyscene->lights) { for (int c = 0; c < 3; ++c) lf.push_back(l.first[c]); for (int c = 0; c < 3; ++c) lf.push_back(l.second[c]); }
+    dump(lights_prefix + ".lights.f32", lf);
+  }
+  flyscene->OUTPUT_BINARY_NAME = out_p6;
   flyscene->raytraceScene();  // key T
   const bool ok = flyscene->lastError().empty();
   if (!ok) fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str());

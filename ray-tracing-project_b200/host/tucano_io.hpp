@@ -419,18 +419,24 @@ inline int ppmQuantise(float c) {
   return std::min(255, (int)s);
 }
 
-// ppmIO.hpp:135-156: ASCII P3, one image row per line, a space after every value
+// ppmIO.hpp:135-156: ASCII P3, one image row per line, a space after every value.  Same bytes as the
+// reference's ofstream << int loop; the 256 in-range values come from a table of ready-made "n " strings.
 inline void writePPMImage(std::string filename, const std::vector<std::vector<Eigen::Vector3f>> &data) {
   if (data.empty()) return;
   int width = (int)data[0].size();
   int height = (int)data.size();
+  char lut[256][4];
+  unsigned char lut_len[256];
+  for (int v = 0; v < 256; ++v) lut_len[v] = (unsigned char)snprintf(lut[v], sizeof lut[v], "%d", v);
   std::string text;
   text.reserve((size_t)width * height * 12 + 32);
   text += "P3\n" + std::to_string(width) + " " + std::to_string(height) + "\n255\n";
   for (int j = 0; j < height; ++j) {
     for (int i = 0; i < width; ++i)
       for (int c = 0; c < 3; ++c) {
-        text += std::to_string(ppmQuantise(data[j][i][c]));
+        const int q = ppmQuantise(data[j][i][c]);
+        if (q >= 0) text.append(lut[q], lut_len[q]);
+        else text += std::to_string(q);  // negative colours and the NaN pixels of SURVEY.md Q8
         text += ' ';
       }
     text += '\n';
@@ -438,6 +444,18 @@ inline void writePPMImage(std::string filename, const std::vector<std::vector<Ei
   std::ofstream out_stream(filename.c_str(), std::ios::binary);
   out_stream.write(text.data(), (std::streamsize)text.size());
   out_stream.close();
+}
+
+// binary P6 of an already quantised image (the device writes these bytes: k_resolve_image /
+// k_untile apply ppmIO.hpp:150's min(255, (int)(255*c)); NaN and negative values are stored as 0).
+inline bool writePPMImageBinary(std::string filename, const unsigned char *rgb8, int width, int height) {
+  if (!rgb8 || width <= 0 || height <= 0) return false;
+  std::ofstream out_stream(filename.c_str(), std::ios::binary);
+  if (!out_stream) return false;
+  out_stream << "P6\n" << width << " " << height << "\n255\n";
+  out_stream.write((const char *)rgb8, (std::streamsize)width * height * 3);
+  out_stream.close();
+  return (bool)out_stream;
 }
 
 }  // namespace ImageImporter

@@ -198,3 +198,46 @@ def test_parallel_obj_ingest_equals_the_line_by_line_loader(name, tmp_path):
         for suffix in DUMPS:
             a, b = np.fromfile(f"{ref}.{suffix}", np.uint32), np.fromfile(f"{pre}.{suffix}", np.uint32)
             assert np.array_equal(a, b), f"{name}: {suffix} differs with {threads} threads / {chunk}-byte ranges"
+
+
+@pytest.mark.gpu
+def test_binary_p6_holds_the_values_of_the_ascii_image(tmp_path):
+    """OUTPUT_BINARY_NAME writes a P6 file of the device-quantised image; its bytes are the
+    numbers result.ppm prints (NaN / negative pixels, printed as INT_MIN or < 0 there, are stored as 0)."""
+    need_cli()
+    c = load_case("dodge_c2")
+    out, p6 = str(tmp_path / "result.ppm"), str(tmp_path / "result_p6.ppm")
+    cmd = [CLI, "--model", model_path("dodgeColorTest"), "--size", "200", "120", "--depth", "4", "--out", out, "--out-p6", p6,
+           "--nolights", "--view"] + [repr(float(x)) for x in c["view"]]
+    for l in c["point_lights"]:
+        cmd += ["--light"] + [repr(float(x)) for x in l]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    w, h, ascii_vals = ppm_values(out)
+    raw = open(p6, "rb").read()
+    header = b"P6\n200 120\n255\n"
+    assert raw.startswith(header) and len(raw) == len(header) + w * h * 3
+    binary_vals = np.frombuffer(raw[len(header):], np.uint8).reshape(h, w, 3)
+    assert np.array_equal(binary_vals, np.clip(ascii_vals, 0, 255))
+
+
+@pytest.mark.gpu
+def test_seeded_soft_light_is_reproducible(tmp_path):
+    """sphericalLightSeeded draws the jittered point lights from a counter-based generator -
+    same seed, same lights, same image; points lie in the cube of sphericalLight (flyscene.cpp:529-538)."""
+    need_cli()
+    imgs, sets = [], []
+    for k, seed in enumerate(("7", "7", "8")):
+        out, pre = str(tmp_path / f"soft{k}.ppm"), str(tmp_path / f"l{k}")
+        cmd = [CLI, "--model", model_path("quirks"), "--size", "48", "40", "--out", out, "--seed", seed, "--dump-lights", pre,
+               "--soft", "-0.5", "2", "3", "0.9", "0.6", "0.3", "0.25", "9"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        imgs.append(ppm_values(out)[2])
+        sets.append(np.fromfile(pre + ".lights.f32", np.float32).reshape(-1, 6))
+    assert sets[0].shape == (10, 6)                                   # 9 jittered points + the light itself
+    assert np.array_equal(sets[0], sets[1]) and np.array_equal(imgs[0], imgs[1])
+    assert not np.array_equal(sets[0][:9, :3], sets[2][:9, :3])
+    d = sets[0][:9, :3] - np.float32([-0.5, 2, 3])
+    assert (np.abs(d) <= 0.25 + 1e-6).all() and len(np.unique(d.round(6), axis=0)) == 9
+    assert np.allclose(sets[0][:, 3:], np.float32([0.9, 0.6, 0.3]) / 10)
