@@ -16,7 +16,7 @@ namespace {
 
 constexpr int kBins = 16;
 constexpr float kCostNode = 1.0f;
-constexpr float kCostTri = 2.0f;  // the exact reference triangle test is ~2-3x a slab pair
+float kCostTri = 2.0f;  // the exact reference triangle test is ~2-3x a slab pair (RTP_SAH_TRI_COST: tuning runs)
 constexpr int kMedianDepth = 32;  // beyond this depth fall back to median splits (bounds the stack)
 
 inline void box_reset(Aabb &b) {
@@ -196,6 +196,7 @@ void build_bvh(const std::vector<Aabb> &prim_bounds, int max_leaf, int n_threads
   out.order.resize(n);
   for (int i = 0; i < n; ++i) out.order[i] = i;
   if (n == 0) return;
+  if (const char *e = std::getenv("RTP_SAH_TRI_COST")) kCostTri = (float)std::atof(e);
   if (max_leaf > 8) max_leaf = 8;
   if (max_leaf < 1) max_leaf = 1;
   if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
