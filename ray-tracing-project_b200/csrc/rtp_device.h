@@ -214,21 +214,7 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
 template <bool ANY>
 RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
   int node = t.node, sp = t.sp;
-  // Speculative descent: the FIRST leaf a lane reaches is set aside (pleaf) and the lane keeps walking inner
-  // nodes; it stops for the triangle tests at its second leaf, at the end of the ray or at the step bound.
-  // Lanes of a warp reach their leaves at unrelated moments, and every stop makes the whole warp wait while a
-  // few lanes run ~100-instruction triangle tests; with one leaf in hand there are half as many stops and
-  // twice as many lanes busy in each.  Hit decisions do not depend on the visiting order (lexicographic
-  // (t, rank) minimum / any hit), so the result is unchanged; a closest-hit ray may look at a few nodes it
-  // would have culled with the postponed leaf's hit already known.  0 = no leaf set aside (0 is the root).
-  int pleaf = 0;
-  for (int trip = 0; node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
-    if (node < 0) {
-      if (pleaf != 0) break;
-      pleaf = node;
-      node = stack[sp--];
-      continue;
-    }
+  for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
     RTP_STAT(nodes);
     float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
@@ -254,10 +240,8 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
       }
     }
   }
-  // leaves: the one set aside first, then the one the descent stopped at and any leaves popped right after it
-  int cur = pleaf != 0 ? pleaf : node;
-  while (cur < 0) {
-    int enc = ~cur;
+  while (node < 0) {
+    int enc = ~node;
     int first = enc >> 3, cnt = (enc & 7) + 1;
     RTP_STAT(leaves);
     for (int k = 0; k < cnt; ++k) {
@@ -275,13 +259,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
       t.sbest = first + k;
       if (ANY) { t.node = kSentinel; t.sp = 0; return true; }
     }
-    if (pleaf != 0) {
-      pleaf = 0;
-      cur = node;  // the descent's own stopping point (a second leaf, an inner node or the end of the ray)
-    } else {
-      node = stack[sp--];
-      cur = node;
-    }
+    node = stack[sp--];
   }
   t.node = node;
   t.sp = sp;
