@@ -66,7 +66,8 @@ def bits_equal(a, b):
     return (a.view(np.int32) == b.view(np.int32)) | (np.isnan(a) & np.isnan(b))
 
 
-HOSTSIM = os.path.join(ROOT, "tests", "hostsim", "libhostsim.so")
+HOSTSIM_DEFS = os.environ.get("HOSTSIM_DEFS", "")  # e.g. -DRTP_BVH4: the same checks on a kernel-variant build
+HOSTSIM = os.path.join(ROOT, "tests", "hostsim", "libhostsim%s.so" % HOSTSIM_DEFS.replace("-D", "_").replace(" ", "").lower())
 
 
 @pytest.fixture(scope="session")
@@ -77,7 +78,7 @@ def hostsim():
                                                                       ("scene_host.cpp", "bvh_build.cpp", "ref_boxes.cpp")]
     deps = srcs + glob.glob(os.path.join(csrc, "*.h"))
     if not os.path.exists(HOSTSIM) or any(os.path.getmtime(d) > os.path.getmtime(HOSTSIM) for d in deps):
-        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-DRTP_TRAV_STATS",
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-DRTP_TRAV_STATS"] + HOSTSIM_DEFS.split() + [
                                "-I/usr/local/cuda/include", "-o", HOSTSIM] + srcs + ["-lpthread"])
     H = C.CDLL(HOSTSIM)
     H.hostsim_create.restype = C.c_char_p
