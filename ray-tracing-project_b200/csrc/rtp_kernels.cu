@@ -526,21 +526,39 @@ __global__ void __launch_bounds__(256) k_resolve(const FrameParams p) {
 // be peer memory on GPU 0, reached over NVLink, and then this kernel IS the framebuffer gather.
 __global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= p.n_px) return;
+  if (r >= p.n_px) return;  // n_px is a multiple of 1024: whole warps leave together
+  const int lane = threadIdx.x & 31;
   const int local = r >> 10, x = r & 31, y = (r >> 5) & 31;
   const int tile = __ldg(p.tile_ids + local);
   const int i = (tile % p.tiles_x) * kTileDim + x, j = (tile / p.tiles_x) * kTileDim + y;
-  if (i >= p.width || j >= p.height) return;
+  const bool valid = i < p.width && j < p.height;
   const int q = (local << 10) + ((((y >> 2) * 4 + (x >> 3)) << 5) + ((y & 3) << 3) + (x & 7));
-  const float4 out = resolve_pixel(p, q);
+  float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (valid) out = resolve_pixel(p, q);
   const size_t idx = (size_t)j * p.width + i;
-  if (p.fb) p.fb[q] = out;
+  if (valid && p.fb) p.fb[q] = out;
   if (p.img_rgb8) {
-    p.img_rgb8[3 * idx] = quantise(out.x);
-    p.img_rgb8[3 * idx + 1] = quantise(out.y);
-    p.img_rgb8[3 * idx + 2] = quantise(out.z);
+    // the warp's 32 pixels are 96 consecutive bytes of one image row: lanes 0-23 store them as 24 aligned words
+    // (one full-width transaction towards HBM, a peer GPU over NVLink or page-locked host memory over PCIe)
+    // instead of 96 single bytes; rows whose start is not word-aligned and the ragged right edge store bytes
+    const unsigned packed = (unsigned)quantise(out.x) | ((unsigned)quantise(out.y) << 8) | ((unsigned)quantise(out.z) << 16);
+    unsigned char *seg = p.img_rgb8 + 3 * (idx - (size_t)lane);  // byte address of the warp's first pixel
+    const bool whole = __all_sync(kFull, valid) && (((size_t)seg & 3) == 0);
+    const int b0 = 4 * (lane < 24 ? lane : 0);  // first byte of this lane's word
+    const int p0 = b0 / 3, c0 = b0 - 3 * p0;
+    const unsigned lo = __shfl_sync(kFull, packed, p0), hi = __shfl_sync(kFull, packed, (p0 + 1) & 31);
+    if (whole) {
+      if (lane < 24) {
+        const unsigned long long both = (unsigned long long)lo | ((unsigned long long)hi << 24);
+        reinterpret_cast<unsigned *>(seg)[lane] = (unsigned)(both >> (8 * c0));
+      }
+    } else if (valid) {
+      p.img_rgb8[3 * idx] = (unsigned char)(packed & 0xff);
+      p.img_rgb8[3 * idx + 1] = (unsigned char)((packed >> 8) & 0xff);
+      p.img_rgb8[3 * idx + 2] = (unsigned char)(packed >> 16);
+    }
   }
-  if (p.img_hit) p.img_hit[idx] = f2i(out.w);
+  if (valid && p.img_hit) p.img_hit[idx] = f2i(out.w);
 }
 
 __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile,

@@ -19,7 +19,7 @@ def scene_for(rtp, case, w, h):
     return s, c
 
 
-@pytest.mark.parametrize("case,w,h,depth", [("dodge_c2", 640, 360, 4), ("testding_2l", 200, 130, 3), ("glas_nan", 96, 96, 2)])
+@pytest.mark.parametrize("case,w,h,depth", [("dodge_c2", 640, 360, 4), ("testding_2l", 203, 130, 3), ("glas_nan", 96, 96, 2)])
 def test_image_does_not_depend_on_the_group_count(rtp, case, w, h, depth):
     s, c = scene_for(rtp, case, w, h)
     ref = None
@@ -30,6 +30,12 @@ def test_image_does_not_depend_on_the_group_count(rtp, case, w, h, depth):
         rows = (h + 31) // 32
         assert s.tile_groups() == (min(g, rows) if g else max(1, min(3, rows * ((w + 31) // 32) // 64)))
         assert np.array_equal(a["rgb8"], b["rgb8"]) and np.array_equal(a["hit"], b["hit"])
+        # page-locked host buffers (what bench.py's e2e leg passes): band copies straight into them
+        import torch
+        pr, ph = torch.zeros(h, w, 3, dtype=torch.uint8).pin_memory(), torch.full((h, w), -7, dtype=torch.int32).pin_memory()
+        z = s.render(w, h, max_depth=depth, want=("rgb8", "hit"), out={"rgb8": pr.numpy(), "hit": ph.numpy()})
+        assert np.array_equal(pr.numpy(), a["rgb8"]) and np.array_equal(ph.numpy(), a["hit"])
+        assert z["stats"]["rays_shadow"] == a["stats"]["rays_shadow"]
         cur = (a["rgb"], a["rgb8"], a["hit"], [a["stats"][k] for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits")])
         if ref is None:
             ref = cur
