@@ -392,11 +392,22 @@ def run_ours(args, wl, rtp):
         dom = "k_trace<closest>" if mc >= ms_ else "k_trace<anyhit>"
         dom_ms, dom_rays = (mc, own[0]) if mc >= ms_ else (ms_, own[1])
         achieved = dom_rays * b_alg(n_tris) / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-        traffic = None
+        traffic, winst = None, None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload, {}).get(dom)
+            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            traffic = tj.get(args.workload, {}).get(dom)
+            winst = tj.get(args.workload + "_warp_instructions", {}).get(dom)
         except Exception:
             pass
+        # issue-rate cross-check: warp instructions of the dominant launch (ncu capture) over its
+        # live duration, against SMs x 4 schedulers x SM clock
+        sm_clock = float((clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6
+        issue_peak = torch.cuda.get_device_properties(local).multi_processor_count * 4 * sm_clock
+        issue = dict(note="traversal is issue/latency bound, not DRAM bound: see profiles/",
+                     grays_per_s_kernel=dom_rays / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0)
+        if winst and dom_ms > 0:
+            issue.update(warp_inst_per_launch=winst, achieved_warp_inst_per_s=winst / (dom_ms / 1e3),
+                         peak_warp_inst_per_s=issue_peak, frac=winst / (dom_ms / 1e3) / issue_peak)
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                     ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
                     dtype="f32", data="synthetic",
@@ -423,8 +434,7 @@ def run_ours(args, wl, rtp):
                                   kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
                                   kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events, the frame as "
                                                   f"one tile group (each kernel alone on the GPU), {float(np.mean(ms_serial)):.4f} ms per step",
-                                  issue=dict(note="traversal is issue/latency bound, not DRAM bound: see profiles/",
-                                             grays_per_s_kernel=dom_rays / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0)))
+                                  issue=issue))
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(wl)
         print(json.dumps(line))
