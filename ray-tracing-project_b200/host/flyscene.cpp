@@ -164,6 +164,7 @@ void Flyscene::raytraceScene(int width, int height) {  // flyscene.cpp:250-297
   PIXEL_COUNT = H;
   if (!OUTPUT_NAME.empty()) Tucano::ImageImporter::writePPMImage(OUTPUT_NAME, pixel_data);  // :292
   if (!OUTPUT_BINARY_NAME.empty()) Tucano::ImageImporter::writePPMImageBinary(OUTPUT_BINARY_NAME, image8.data(), W, H);
+  if (!OUTPUT_PNG_NAME.empty()) Tucano::ImageImporter::writePNGImage(OUTPUT_PNG_NAME, image8.data(), W, H);
   const time_t end_time = time(NULL);
   std::cout << "ray tracing done! " << std::endl;
   std::cout << "Runtime: " << (end_time - start_time) << " seconds (device " << last_stats.ms_total << " ms, "

@@ -124,6 +124,7 @@ class Flyscene {
   std::string OBJECT_NAME = "dodgeColorTest.obj";
   std::string MODEL_DIR = "resources/models/";  // cwd-relative, as flyscene.cpp:18
   std::string OUTPUT_NAME = "result.ppm";       // flyscene.cpp:292; empty: no file
+  std::string OUTPUT_PNG_NAME = "";             // non-empty: also write an 8-bit RGB PNG of it
   std::string OUTPUT_BINARY_NAME = "";          // non-empty: also write a binary P6 PPM of the device-quantised image
   int DEVICE = -1;                               // CUDA ordinal (-1: current device)
 

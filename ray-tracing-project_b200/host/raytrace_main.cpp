@@ -6,10 +6,11 @@
 //            [--view m0..m11] [--light x y z r g b]... [--dirlight x y z r g b]... [--nolights]
 //            [--soft x y z r g b RADIUS N] [--seed S]   soft light: N jittered point lights (libc rand, or with --seed
 //                                            the counter-based generator of Flyscene::sphericalLightSeeded)
-//            [--out result.ppm] [--out-p6 result_p6.ppm] [--device N] [--dump-scene PREFIX] [--dump-lights PREFIX]
+//            [--out result.ppm] [--out-p6 result_p6.ppm] [--out-png result.png] [--device N] [--dump-scene PREFIX] [--dump-lights PREFIX]
 //            [--serial-obj]                  with --dump-scene: the line-by-line OBJ loader instead of the parallel one
 //            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
 //            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
+//            [--png-from-u8 IN.u8 OUT.png]   W*H*3 bytes -> PNG (no GPU)
 #include <array>
 #include <chrono>
 #include <climits>
@@ -138,7 +139,7 @@ int ppm_from_f32(const std::string &in, const std::string &out, int W, int H) {
 }  // namespace
 
 int main(int argc, char **argv) {
-  std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out, out_p6, lights_prefix;
+  std::string model = "resources/models/dodgeColorTest.obj", out = "result.ppm", dump_prefix, rays_prefix, f32_in, f32_out, out_p6, out_png, u8_in, u8_out, lights_prefix;
   unsigned long long seed = 0;
   bool seeded = false;
   int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
@@ -157,6 +158,8 @@ int main(int argc, char **argv) {
     else if (a == "--device") { need(i, 1); device = atoi(argv[++i]); }
     else if (a == "--out") { need(i, 1); out = argv[++i]; }
     else if (a == "--out-p6") { need(i, 1); out_p6 = argv[++i]; }
+    else if (a == "--out-png") { need(i, 1); out_png = argv[++i]; }
+    else if (a == "--png-from-u8") { need(i, 2); u8_in = argv[++i]; u8_out = argv[++i]; }
     else if (a == "--seed") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); seeded = true; }
     else if (a == "--dump-lights") { need(i, 1); lights_prefix = argv[++i]; }
     else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
@@ -181,6 +184,13 @@ int main(int argc, char **argv) {
   if (!dump_prefix.empty()) return dump_scene(model, dump_prefix, 300, serial_obj, load_only);
   if (!rays_prefix.empty()) return dump_rays(rays_prefix, W, H, fovy, has_view ? view : nullptr);
   if (!f32_in.empty()) return ppm_from_f32(f32_in, f32_out, W, H);
+  if (!u8_in.empty()) {  // W*H*3 bytes -> PNG (no GPU): the writer's own test hook
+    std::vector<unsigned char> px((size_t)W * H * 3);
+    FILE *f = fopen(u8_in.c_str(), "rb");
+    if (!f || fread(px.data(), 1, px.size(), f) != px.size()) { if (f) fclose(f); return 1; }
+    fclose(f);
+    return Tucano::ImageImporter::writePNGImage(u8_out, px.data(), W, H) ? 0 : 1;
+  }
 
   Flyscene *flyscene = new Flyscene();  // main.cpp:40-41
   const size_t slash = model.find_last_of('/');
@@ -214,6 +224,7 @@ int main(int argc, char **argv) {
     dump(lights_prefix + ".lights.f32", lf);
   }
   flyscene->OUTPUT_BINARY_NAME = out_p6;
+  flyscene->OUTPUT_PNG_NAME = out_png;
   flyscene->raytraceScene();  // key T
   const bool ok = flyscene->lastError().empty();
   if (!ok) fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str());

@@ -458,6 +458,65 @@ inline bool writePPMImageBinary(std::string filename, const unsigned char *rgb8,
   return (bool)out_stream;
 }
 
+// PNG of the same quantised image (8-bit RGB, filter 0, stored deflate blocks: no compression library needed).
+inline bool writePNGImage(std::string filename, const unsigned char *rgb8, int width, int height) {
+  if (!rgb8 || width <= 0 || height <= 0) return false;
+  static unsigned crc_table[256];
+  static bool have_table = false;
+  if (!have_table) {
+    for (unsigned n = 0; n < 256; ++n) {
+      unsigned c = n;
+      for (int k = 0; k < 8; ++k) c = (c & 1) ? 0xedb88320u ^ (c >> 1) : c >> 1;
+      crc_table[n] = c;
+    }
+    have_table = true;
+  }
+  auto be32 = [](std::string &o, unsigned v) { for (int k = 3; k >= 0; --k) o += (char)((v >> (8 * k)) & 0xff); };
+  auto chunk = [&](std::string &o, const char *type, const std::string &data) {
+    be32(o, (unsigned)data.size());
+    std::string body = std::string(type, 4) + data;
+    unsigned c = 0xffffffffu;
+    for (unsigned char ch : body) c = crc_table[(c ^ ch) & 0xff] ^ (c >> 8);
+    o += body;
+    be32(o, c ^ 0xffffffffu);
+  };
+  // raw scanlines: filter byte 0 + W*3 bytes
+  const size_t row = (size_t)width * 3 + 1, raw_size = row * (size_t)height;
+  std::string raw(raw_size, '\0');
+  for (int j = 0; j < height; ++j) std::memcpy(&raw[(size_t)j * row + 1], rgb8 + (size_t)j * width * 3, (size_t)width * 3);
+  unsigned a = 1, b = 0;  // Adler-32 of the raw data
+  for (size_t i = 0; i < raw_size;) {
+    const size_t n = std::min<size_t>(5552, raw_size - i);
+    for (size_t k = 0; k < n; ++k) { a += (unsigned char)raw[i + k]; b += a; }
+    a %= 65521u; b %= 65521u;
+    i += n;
+  }
+  std::string z;
+  z.reserve(raw_size + raw_size / 65535 * 5 + 16);
+  z += (char)0x78; z += (char)0x01;
+  for (size_t i = 0; i < raw_size;) {
+    const size_t n = std::min<size_t>(65535, raw_size - i);
+    z += (char)(i + n == raw_size ? 1 : 0);  // BFINAL, BTYPE = 00 (stored)
+    z += (char)(n & 0xff); z += (char)(n >> 8);
+    z += (char)(~n & 0xff); z += (char)((~n >> 8) & 0xff);
+    z.append(raw, i, n);
+    i += n;
+  }
+  be32(z, (b << 16) | a);
+  std::string out("\x89PNG\r\n\x1a\n", 8);
+  std::string ihdr;
+  be32(ihdr, (unsigned)width); be32(ihdr, (unsigned)height);
+  ihdr += (char)8; ihdr += (char)2; ihdr += (char)0; ihdr += (char)0; ihdr += (char)0;  // 8-bit, RGB
+  chunk(out, "IHDR", ihdr);
+  chunk(out, "IDAT", z);
+  chunk(out, "IEND", std::string());
+  std::ofstream f(filename.c_str(), std::ios::binary);
+  if (!f) return false;
+  f.write(out.data(), (std::streamsize)out.size());
+  f.close();
+  return (bool)f;
+}
+
 }  // namespace ImageImporter
 
 }  // namespace Tucano

@@ -206,8 +206,9 @@ def test_binary_p6_holds_the_values_of_the_ascii_image(tmp_path):
     numbers result.ppm prints (NaN / negative pixels, printed as INT_MIN or < 0 there, are stored as 0)."""
     need_cli()
     c = load_case("dodge_c2")
-    out, p6 = str(tmp_path / "result.ppm"), str(tmp_path / "result_p6.ppm")
+    out, p6, png = str(tmp_path / "result.ppm"), str(tmp_path / "result_p6.ppm"), str(tmp_path / "result.png")
     cmd = [CLI, "--model", model_path("dodgeColorTest"), "--size", "200", "120", "--depth", "4", "--out", out, "--out-p6", p6,
+           "--out-png", png,
            "--nolights", "--view"] + [repr(float(x)) for x in c["view"]]
     for l in c["point_lights"]:
         cmd += ["--light"] + [repr(float(x)) for x in l]
@@ -219,6 +220,7 @@ def test_binary_p6_holds_the_values_of_the_ascii_image(tmp_path):
     assert raw.startswith(header) and len(raw) == len(header) + w * h * 3
     binary_vals = np.frombuffer(raw[len(header):], np.uint8).reshape(h, w, 3)
     assert np.array_equal(binary_vals, np.clip(ascii_vals, 0, 255))
+    assert np.array_equal(read_png_rgb8(png), binary_vals)
 
 
 @pytest.mark.gpu
@@ -241,3 +243,34 @@ def test_seeded_soft_light_is_reproducible(tmp_path):
     d = sets[0][:9, :3] - np.float32([-0.5, 2, 3])
     assert (np.abs(d) <= 0.25 + 1e-6).all() and len(np.unique(d.round(6), axis=0)) == 9
     assert np.allclose(sets[0][:, 3:], np.float32([0.9, 0.6, 0.3]) / 10)
+
+
+def read_png_rgb8(path):
+    """Minimal PNG reader for the writer's output (8-bit RGB, filter 0): checks signature, CRCs and sizes."""
+    import struct
+    import zlib
+    raw = open(path, "rb").read()
+    assert raw[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, chunks = 8, []
+    while pos < len(raw):
+        n, typ = struct.unpack(">I4s", raw[pos:pos + 8])
+        data = raw[pos + 8:pos + 8 + n]
+        assert struct.unpack(">I", raw[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(typ + data) & 0xffffffff
+        chunks.append((typ, data))
+        pos += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    w, h, depth, ctype, comp, filt, inter = struct.unpack(">IIBBBBB", chunks[0][1])
+    assert (depth, ctype, comp, filt, inter) == (8, 2, 0, 0, 0)
+    rows = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(h, 1 + 3 * w)
+    assert (rows[:, 0] == 0).all()
+    return rows[:, 1:].reshape(h, w, 3)
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 5), (300, 200)])   # 300x200: more than one stored deflate block
+def test_png_writer_roundtrip(w, h, tmp_path):
+    need_cli()
+    px = np.random.default_rng(w * h).integers(0, 256, (h, w, 3), dtype=np.uint8)
+    px.tofile(tmp_path / "in.u8")
+    out = str(tmp_path / "o.png")
+    assert subprocess.run([CLI, "--size", str(w), str(h), "--png-from-u8", str(tmp_path / "in.u8"), out]).returncode == 0
+    assert np.array_equal(read_png_rgb8(out), px)
