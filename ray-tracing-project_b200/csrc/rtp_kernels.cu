@@ -586,11 +586,16 @@ int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning 
 // Straggler policy (measured on B200, profiles/r01_tail.md): parking pays for closest-hit launches on
 // scenes that do not fit the L2 (cold nodes make the serial chain slow: C3 closest-hit 0.47 -> 0.40 ms);
 // on L2-resident scenes and for shadow rays k_coop's launch costs more than the shorter tail saves.
-int g_budget = 12;      // RTP_BUDGET: steps before the last lanes of a warp count as stragglers (0: never park)
-int g_park_lanes = 4;   // RTP_PARK_LANES: ... when at most this many lanes are left
-int g_park_any = 0;     // RTP_PARK_ANY=1: park shadow rays too
-int g_budget_any = 12;  // RTP_BUDGET_ANY: step budget of shadow-ray launches (a step of an unoccluded ray is 32 nodes)
-int g_park_lanes_any = 4;
+// v5 sweep (profiles/r01_parking.md): every ray still running after 6 steps is parked, however many lanes are left
+// (C3 frame 0.770 -> 0.735 ms, one rank's 1/8 share 0.328 -> 0.255 ms); shadow rays only in small launches, where
+// the launch is as long as its longest ray (1/8 share 0.255 -> 0.23 ms) - in a full-frame launch their k_coop pass
+// costs more than the tail it removes (0.735 -> 0.79 ms).
+int g_budget = 6;       // RTP_BUDGET: steps a warp spends on a batch before the rays still running are parked (0: never)
+int g_park_lanes = 32;  // RTP_PARK_LANES: ... if at most this many lanes are still running
+int g_park_any = 0;     // RTP_PARK_ANY=1: park shadow rays in every launch
+int g_any_small = 400000;  // RTP_ANY_SMALL: ... or in launches over at most this many paths
+int g_budget_any = 6;   // RTP_BUDGET_ANY: step budget of shadow-ray launches (a step of an unoccluded ray is 32 nodes)
+int g_park_lanes_any = 32;
 int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
 
 // Refill policy: a warp refills its idle lanes from the global ray list when fewer than `refill`
@@ -600,16 +605,15 @@ int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
 // keep at least 24 lanes busy.
 template <class Job>
 int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters, int launch_slot, bool coherent,
-                 cudaStream_t st) {
+                 long long n_paths, cudaStream_t st) {
   const int threads = cfg.threads;
   if (g_refill == -2) {
     const char *e = std::getenv("RTP_REFILL");
     g_refill = e ? std::atoi(e) : -1;
-    if ((e = std::getenv("RTP_BUDGET"))) g_budget = std::atoi(e);
-    if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = std::atoi(e);
+    if ((e = std::getenv("RTP_BUDGET"))) g_budget = g_budget_any = std::atoi(e);
+    if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = g_park_lanes_any = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_ANY"))) g_park_any = std::atoi(e);
-    g_budget_any = g_budget;
-    g_park_lanes_any = g_park_lanes;
+    if ((e = std::getenv("RTP_ANY_SMALL"))) g_any_small = std::atoi(e);
     if ((e = std::getenv("RTP_BUDGET_ANY"))) g_budget_any = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_LANES_ANY"))) g_park_lanes_any = std::atoi(e);
     if ((e = std::getenv("RTP_PARK_SMALL"))) g_park_small = std::atoi(e);
@@ -627,7 +631,8 @@ int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters
   pl.slots = cfg.park_slots;
   pl.ctr = counters + kCtrPark + 2 * launch_slot;
   pl.cap = cfg.park_cap;
-  const bool park = g_budget > 0 && cfg.park_slots && (!Job::kAny || g_park_any) && (cfg.scene_exceeds_l2 || g_park_small);
+  const bool park = g_budget > 0 && cfg.park_slots && (!Job::kAny || g_park_any || n_paths <= g_any_small) &&
+                    (cfg.scene_exceeds_l2 || g_park_small);
   pl.budget = park ? (Job::kAny ? g_budget_any : g_budget) : 0x3fffffff;
   pl.lanes = Job::kAny ? g_park_lanes_any : g_park_lanes;
   if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job, pl);
@@ -671,7 +676,7 @@ int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaSt
   j.cursor = p.counters + kCtrFetchClosest + depth;
   j.count_ptr = depth == 0 ? nullptr : p.counters + kCtrPaths + depth;
   j.count_fixed = p.n_px;
-  return launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, st);
+  return launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, p.n_px, st);
 }
 
 void launch_prep(const FrameParams &p, int depth, cudaStream_t st) {
@@ -685,7 +690,7 @@ int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStr
   j.occl = p.occl;
   j.cursor = p.counters + kCtrFetchAny + depth;
   j.hits_ptr = p.counters + kCtrHits + depth;
-  return launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, st);
+  return launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, p.n_px, st);
 }
 
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
@@ -709,14 +714,14 @@ int launch_rays_closest(const DeviceScene &S, const float *rays, long long n, in
                          const LaunchCfg &cfg, cudaStream_t st) {
   RaysClosest j;
   j.S = S; j.rays = rays; j.face = face; j.tout = t; j.cursor = cursor; j.n = (int)n;
-  return launch_trace(j, cfg.blocks_closest, cfg, cursor - kCtrAux, 16, false, st);
+  return launch_trace(j, cfg.blocks_closest, cfg, cursor - kCtrAux, 16, false, n, st);
 }
 
 int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st) {
   RaysAny j;
   j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
-  return launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, st);
+  return launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, 1ll << 40, st);  // ray batches: never (C5)
 }
 
 }  // namespace rtp
