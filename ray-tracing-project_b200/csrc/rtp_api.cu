@@ -105,6 +105,7 @@ struct rtp_scene {
   } aslot[2];
   cudaStream_t cstream[kMaxGroups] = {};
   cudaEvent_t resolved[kMaxGroups] = {};
+  int *counters_pinned = nullptr;           // page-locked landing place of a frame's counters (rtp_render)
   unsigned async_head = 0, async_tail = 0;  // frames enqueued / waited for
   bool in_async_call = false;
   int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
@@ -273,6 +274,7 @@ int rtp_scene_destroy(rtp_scene *s) {
     if (s->cstream[i]) { cudaStreamSynchronize(s->cstream[i]); cudaStreamDestroy(s->cstream[i]); }
     if (s->resolved[i]) cudaEventDestroy(s->resolved[i]);
   }
+  if (s->counters_pinned) cudaFreeHost(s->counters_pinned);
   for (auto &a : s->aslot) {
     if (a.counters_host) cudaFreeHost(a.counters_host);
     if (a.ev0) cudaEventDestroy(a.ev0);
@@ -801,11 +803,21 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
   CK(cudaEventRecord(s->ev[1], cs));
   if (banded) {
     CK(cudaEventRecord(s->ev[2], cs));
+    // the frame's counters ride behind the frame on the same stream: one host wait for image and statistics
+    const bool quick_stats = st && !(o->flags & RTP_RENDER_PROFILE);
+    if (quick_stats) {
+      if (!s->counters_pinned) CK(cudaHostAlloc((void **)&s->counters_pinned, sizeof(int) * kCtrInts * kMaxGroups, cudaHostAllocDefault));
+      CK(cudaMemcpyAsync(s->counters_pinned, s->counters.p, sizeof(int) * kCtrInts * (size_t)s->last_groups, cudaMemcpyDeviceToHost, cs));
+    }
     CK(cudaStreamSynchronize(cs));
     if (st) {
       std::memset(st, 0, sizeof *st);
-      rc = read_stats(s, st, cs);
-      if (rc) return rc;
+      if (quick_stats) {
+        stats_from_counters(s, s->counters_pinned, std::max(s->last_groups, 1), s->last_primary, s->last_depth, s->last_lights, st);
+      } else {
+        rc = read_stats(s, st, cs);
+        if (rc) return rc;
+      }
       CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // includes the overlapped band copies
       st->ms_total = st->ms_trace;
       st->kernel_launches = launches;
