@@ -264,13 +264,13 @@ def run_ours(args, wl, rtp):
     def step(profile=False):
         flags = rtp.RENDER_PROFILE if profile else 0
         if peer:
-            mg.render_frame_peer(scene, img, md, stream, flags=flags)
+            mg.render_frame_peer(scene, img, md, stream, flags=flags, barrier=args.barrier)
         else:
             mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None, flags=flags)
 
     # both routes must deliver the same bytes
     mg.render_frame(scene, tg, md, stream, d_rgb8=rgb8.data_ptr() if rank == 0 else None)
-    mg.render_frame_peer(scene, img, md, stream)
+    mg.render_frame_peer(scene, img, md, stream, barrier=args.barrier)
     torch.cuda.synchronize()
     same = bool(torch.equal(img.rgb8_tensor(img.frame - 1).reshape(-1), rgb8)) if rank == 0 else True
     if not same:
@@ -375,6 +375,8 @@ def run_ours(args, wl, rtp):
                          "host uint8 image per frame",
                     image_equals_sync=bool(torch.equal(host2[0], host2[1])))
 
+    if world > 1 and scene.peer_barrier_timeouts() != 0:
+        raise SystemExit("bench.py: a frame barrier timed out (a rank did not arrive)")
     if rank == 0:
         total_ms = sum(ms_steps)
         value = rays_frame * args.steps / (total_ms / 1e3) / 1e6
@@ -413,7 +415,9 @@ def run_ours(args, wl, rtp):
                     dtype="f32", data="synthetic",
                     config=dict(workload=wl["desc"], rays_per_frame=rays_frame, triangles=n_tris, bvh_nodes=info["n_bvh_nodes"],
                                 parallelism=f"tile{world}" if world > 1 else "1gpu",
-                                gather=("resolve kernel stores tiles into GPU 0's image (CUDA IPC peer memory) + 4-byte all-reduce"
+                                gather=("resolve kernel stores tiles into GPU 0's image (CUDA IPC peer memory) + " +
+                                        ("own one-thread barrier kernel on a counter in GPU 0's memory" if args.barrier == "peer"
+                                         else "4-byte NCCL all-reduce")
                                         if peer else "NCCL gather of tile buffers + un-tile kernel") if world > 1 else
                                        "resolve kernel writes the image (1 GPU)" if peer else "un-tile kernel (1 GPU)",
                                 peer_image_equals_nccl_gather=same,
@@ -595,6 +599,8 @@ def main():
     ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"])
+    ap.add_argument("--barrier", default="peer", choices=["peer", "nccl"],
+                    help="frame barrier of the peer-store route: the library's own kernel over peer memory, or a 4-byte NCCL all-reduce")
     args = ap.parse_args()
     rtp = importlib.import_module("ray-tracing-project_b200")
     synth = importlib.import_module("ray-tracing-project_b200.synth")

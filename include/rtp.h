@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 4
+#define RTP_ABI_VERSION 5
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -179,6 +179,16 @@ int rtp_render_image_device(rtp_scene *s, const rtp_render_opts *o, void *d_rgb8
 int rtp_shared_alloc(int device, size_t bytes, void **d_ptr, void *handle /* RTP_SHARED_HANDLE_BYTES */);
 int rtp_shared_open(int device, const void *handle, void **d_ptr);
 int rtp_shared_free(int device, void *d_ptr, int opened /* 1: came from rtp_shared_open */);
+
+/* Frame barrier of the peer-store route, made of the library's own kernel instead of a collective: `d_counter` is a
+ * zero-initialised uint32 in memory every rank can reach (e.g. the tail of GPU 0's rtp_shared_alloc block).  Enqueued
+ * on `stream` behind this rank's frame, one thread publishes the rank's image stores, adds 1 to the counter with a
+ * system-scope atomic over NVLink and waits until it has reached `target` (= world x frame number, frames counted
+ * from 1; the counter is never reset).  Work enqueued behind it on GPU 0 sees every rank's pixels.  A wait that is not
+ * satisfied within timeout_ms gives up (no hang) and is counted: rtp_peer_barrier_timeouts (synchronises the device)
+ * returns how many did, or a negative rtp_status.  Replaces the join of raytraceScene's threads (flyscene.cpp:287-289). */
+int rtp_peer_barrier(rtp_scene *s, void *d_counter, uint32_t target, int timeout_ms, void *stream);
+int rtp_peer_barrier_timeouts(rtp_scene *s);
 
 /* ---- single-ray API ---------------------------------------------------------------------- */
 typedef enum rtp_ray_mode {

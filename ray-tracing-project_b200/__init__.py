@@ -61,7 +61,7 @@ class RtpStats(C.Structure):
 EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_camera", "rtp_render",
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
-           "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_render_async", "rtp_render_wait", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
+           "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_render_async", "rtp_render_wait", "rtp_peer_barrier", "rtp_peer_barrier_timeouts", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
            "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free"]
 
 _lib = None
@@ -90,6 +90,8 @@ def lib():
         L.rtp_get_tile_groups.argtypes = [C.c_void_p]
         L.rtp_render_async.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p]
         L.rtp_render_wait.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
+        L.rtp_peer_barrier.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+        L.rtp_peer_barrier_timeouts.argtypes = [C.c_void_p]
         L.rtp_render.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.POINTER(RtpStats)]
         L.rtp_render_tiles_device.argtypes = [C.c_void_p, C.POINTER(RtpRenderOpts), C.c_void_p, C.c_void_p,
@@ -272,6 +274,16 @@ class Scene:
         st = RtpStats()
         self._check(self._L.rtp_render_wait(self._h, C.byref(st)))
         return st.as_dict()
+
+    def peer_barrier(self, d_counter, target, timeout_ms=2000, stream=None):
+        """rtp_peer_barrier: arrive at and wait on a counter in (peer) device memory, enqueued on `stream`."""
+        self._check(self._L.rtp_peer_barrier(self._h, d_counter, int(target) & 0xffffffff, int(timeout_ms), stream))
+
+    def peer_barrier_timeouts(self):
+        n = self._L.rtp_peer_barrier_timeouts(self._h)
+        if n < 0:
+            self._check(n)
+        return n
 
     def render_tiles_device(self, w, h, d_tiles_ptr, max_depth=2, background=BACKGROUND, rank=0, world=1,
                             stream=None, want_stats=False, flags=0):

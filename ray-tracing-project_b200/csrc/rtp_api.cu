@@ -83,6 +83,7 @@ struct rtp_scene {
   DevBuf<int> face_of;
   DevBuf<int> counters;
   DevBuf<int> park;  // parked-ray list of the trace kernels
+  DevBuf<int> barrier_timeouts;  // [1] waits of rtp_peer_barrier that gave up
   DeviceScene dS;
   std::vector<float4> lights_host;  // what s->lights holds
   DeviceCamera cam;
@@ -714,6 +715,29 @@ int rtp_shared_alloc(int device, size_t bytes, void **d_ptr, void *handle) {
   }
   std::memcpy(handle, &h, sizeof h);
   return RTP_OK;
+}
+
+int rtp_peer_barrier(rtp_scene *s, void *d_counter, uint32_t target, int timeout_ms, void *stream) {
+  if (!s || !d_counter || timeout_ms <= 0) return fail(RTP_ERR_INVALID, "rtp_peer_barrier: bad argument");
+  if (((size_t)d_counter & 3) != 0) return fail(RTP_ERR_INVALID, "rtp_peer_barrier: counter must be 4-byte aligned");
+  DeviceGuard g(s->device);
+  if (!s->barrier_timeouts.p) {
+    CK(s->barrier_timeouts.ensure(1));
+    CK(cudaMemset(s->barrier_timeouts.p, 0, sizeof(int)));
+  }
+  launch_peer_barrier((unsigned *)d_counter, target, (unsigned long long)timeout_ms * 1000000ull, s->barrier_timeouts.p,
+                      (cudaStream_t)stream);
+  CK(cudaGetLastError());
+  return RTP_OK;
+}
+
+int rtp_peer_barrier_timeouts(rtp_scene *s) {
+  if (!s) return fail(RTP_ERR_INVALID, "rtp_peer_barrier_timeouts: null scene");
+  if (!s->barrier_timeouts.p) return 0;
+  DeviceGuard g(s->device);
+  int n = 0;
+  CK(cudaMemcpy(&n, s->barrier_timeouts.p, sizeof n, cudaMemcpyDeviceToHost));  // waits for the device
+  return n;
 }
 
 int rtp_shared_open(int device, const void *handle, void **d_ptr) {

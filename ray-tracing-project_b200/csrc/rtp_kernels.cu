@@ -582,6 +582,31 @@ __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_s
   if (hit) hit[idx] = f2i(v.w);
 }
 
+// Frame barrier over peer memory.  `counter` lives in GPU 0's shared image block (CUDA IPC); every rank's frame ends
+// with one thread that publishes the rank's image stores (they were made by earlier kernels of this stream, so they
+// are complete; the fence orders them before the arrival for every observer in the system), adds 1 to the counter
+// with a system-scope atomic over NVLink, and then polls it until all `world` ranks of this frame have arrived.
+// The counter only ever grows (target = world * frame number), so there is no reset to race with.  A rank that never
+// arrives does not hang the others: after timeout_ns the wait gives up and counts the event in *timeouts.
+__global__ void k_peer_barrier(unsigned *counter, unsigned target, unsigned long long timeout_ns, int *timeouts) {
+  __threadfence_system();
+  atomicAdd_system(counter, 1u);
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+    if ((int)(v - target) >= 0) break;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > timeout_ns) {
+      atomicAdd(timeouts, 1);
+      break;
+    }
+    __nanosleep(100);
+  }
+  __threadfence_system();
+}
+
 int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning runs)
 // Straggler policy (measured on B200, profiles/r01_tail.md): parking pays for closest-hit launches on
 // scenes that do not fit the L2 (cold nodes make the serial chain slow: C3 closest-hit 0.47 -> 0.40 ms);
@@ -661,6 +686,10 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
   cfg.blocks_coop = sms * 2;
+}
+
+void launch_peer_barrier(unsigned *counter, unsigned target, unsigned long long timeout_ns, int *timeouts, cudaStream_t st) {
+  k_peer_barrier<<<1, 1, 0, st>>>(counter, target, timeout_ns, timeouts);
 }
 
 void launch_raygen(const FrameParams &p, cudaStream_t st) { k_raygen<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }

@@ -71,6 +71,9 @@ void launch_resolve(const FrameParams &p, cudaStream_t st);
 void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile, int width, int height,
                    int world, int only_rank, float *rgb, unsigned char *rgb8, int *hit, cudaStream_t st);
 
+// arrive-and-wait of one rank on a counter in (peer) device memory; see k_peer_barrier
+void launch_peer_barrier(unsigned *counter, unsigned target, unsigned long long timeout_ns, int *timeouts, cudaStream_t st);
+
 // ray-batch API (rtp_trace_rays): rays = n x (o, d) floats on the device
 int launch_rays_closest(const DeviceScene &S, const float *rays, long long n, int *face, float *t, int *cursor,
                          const LaunchCfg &cfg, cudaStream_t st);

@@ -9,7 +9,7 @@ Two ways to bring the tiles to GPU 0:
   * PeerImage + render_frame_peer: rank 0's image is mapped into every process through CUDA IPC and
     each rank's resolve kernel stores its finished pixels straight into it over NVLink
     (rtp_render_image_device) - the gather is fused into the last kernel of the frame; what is left
-    of the collective is a barrier.  The image is double-buffered so that rank 0 may still read
+    of the collective is a barrier, and that is the library's own kernel too (rtp_peer_barrier).  The image is double-buffered so that rank 0 may still read
     frame f while the others already write frame f + 1.
 
 This is plumbing only: buffers, the collective, call order.  The pixels come from the library
@@ -64,7 +64,7 @@ class PeerImage:
         handle = torch.zeros(self.rtp.SHARED_HANDLE_BYTES, dtype=torch.uint8, device=torch.device("cuda", device_index))
         self.opened = False
         if rank == 0:
-            self.base, raw = self.rtp.shared_alloc(device_index, 2 * self.stride)
+            self.base, raw = self.rtp.shared_alloc(device_index, 2 * self.stride + 256)  # + the frame-barrier counter (zeroed)
             handle.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
         if world > 1:
             dist.broadcast(handle, src=0)
@@ -73,6 +73,7 @@ class PeerImage:
             self.opened = True
         self.frame = 0
         self.token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
+        self.counter = self.base + 2 * self.stride  # uint32 in rank 0's memory, reached by every rank over NVLink
 
     def planes(self, frame=None):
         """(rgb8 pointer, hit pointer or None) of the buffer frame `frame` is written to."""
@@ -94,16 +95,21 @@ class PeerImage:
             self.base = None
 
 
-def render_frame_peer(scene, img, max_depth, stream, flags=0):
-    """One frame: every rank renders its tiles and resolves them straight into rank 0's image (peer
-    stores over NVLink); a 4-byte all-reduce orders rank 0's readers after everybody's stores.  Returns the
-    (rgb8, hit) device pointers of the finished frame (meaningful on rank 0)."""
+def render_frame_peer(scene, img, max_depth, stream, flags=0, barrier="peer", timeout_ms=2000):
+    """One frame: every rank renders its tiles and resolves them straight into rank 0's image (peer stores over
+    NVLink), then arrives at the frame barrier.  barrier = "peer": the library's own one-thread kernel
+    (rtp_peer_barrier: system-scope atomic + wait on a counter in rank 0's memory; no collective left on this route);
+    "nccl": a 4-byte all-reduce as a stream-ordered barrier.  Either way work enqueued behind it on rank 0 sees
+    everybody's pixels, no rank overwrites a buffer rank 0 may still read (the image is double-buffered and a rank
+    cannot start frame f + 2 before every rank has finished frame f + 1), and the host is not blocked.
+    Returns the (rgb8, hit) device pointers of the finished frame (meaningful on rank 0)."""
     d_rgb8, d_hit = img.planes()
     scene.render_image_device(img.w, img.h, d_rgb8=d_rgb8, d_hit=d_hit, max_depth=max_depth, rank=img.rank,
                               world=img.world, stream=stream, flags=flags)
-    if img.world > 1:
-        # a 4-byte all-reduce as a stream-ordered barrier: it starts after this rank's stores (same stream)
-        # and completes on rank 0 only when every rank has started it; the host is not blocked
-        dist.all_reduce(img.token)
     img.frame += 1
+    if img.world > 1:
+        if barrier == "peer":
+            scene.peer_barrier(img.counter, img.world * img.frame, timeout_ms, stream)
+        else:
+            dist.all_reduce(img.token)
     return d_rgb8, d_hit

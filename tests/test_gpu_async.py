@@ -77,4 +77,35 @@ def test_async_call_order_is_checked(rtp):
     assert np.array_equal(buf[0].numpy(), buf[1].numpy())
     out = s.render(64, 64, want=("rgb8",))
     assert np.array_equal(out["rgb8"], buf[0].numpy())
+    # pageable host memory works too (the copies then block the caller instead of overlapping)
+    plain, plain_hit = np.zeros((64, 64, 3), np.uint8), np.zeros((64, 64), np.int32)
+    s.render_async(64, 64, plain.ctypes.data, plain_hit.ctypes.data)
+    st = s.render_wait()
+    assert np.array_equal(plain, out["rgb8"]) and st["rays_primary"] == 64 * 64
+    assert np.array_equal(plain_hit, s.render(64, 64, want=("hit",))["hit"])
+    s.close()
+
+
+def test_peer_barrier_kernel_arrives_waits_and_times_out(rtp):
+    """rtp_peer_barrier on one GPU: a satisfied target passes at once, the counter only grows, and a rank that never
+    arrives costs the others a bounded wait (counted), not a hang."""
+    import time
+    import torch
+    c = load_case("plane_c1")
+    m = load_golden_mesh("plane")
+    s = rtp.Scene(m.verts, m.normals, m.faces, m.face_mat, m.materials, m.shape)
+    counter = torch.zeros(64, dtype=torch.int32, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    for frame in (1, 2, 3):                       # world = 1: the rank's own arrival satisfies the target
+        s.peer_barrier(counter.data_ptr(), frame, 500, stream)
+    torch.cuda.synchronize()
+    assert int(counter[0].item()) == 3 and s.peer_barrier_timeouts() == 0
+    t0 = time.perf_counter()
+    s.peer_barrier(counter.data_ptr(), 2 * 4, 50, stream)   # "world = 2", frame 4: the other rank never comes
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    assert 0.04 < dt < 1.0, dt
+    assert int(counter[0].item()) == 4 and s.peer_barrier_timeouts() == 1
+    with pytest.raises(rtp.RtpError):
+        s.peer_barrier(counter.data_ptr() + 2, 1, 50, stream)  # misaligned counter
     s.close()
