@@ -211,8 +211,11 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
 // A step visits at most kMaxNodesPerStep inner nodes (it is resumable: t.node = the next inner node),
 // so that a ray with a long leaf-free stretch - an unoccluded shadow ray - still comes back to the
 // caller, who may hand a straggler to the whole warp (rtp_kernels.cu).
-template <bool ANY>
-RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
+// box_origin: callable returning the origin for the reference box test.  It is evaluated only when a candidate
+// face has to be filtered (for a frame's shadow rays it is a division and a global load that a step otherwise
+// paid on entry, every time).
+template <bool ANY, class BoxOrigin>
+RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_origin) {
   int node = t.node, sp = t.sp;
   for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
@@ -253,7 +256,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, v3 bo) {
       // tt <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
       // and t == +inf never beats the initial INFINITY.
       if (!ANY && !(tt < t.tbest || (t.sbest >= 0 && rank < t.rbest))) continue;
-      if ((ANY || t.careful) && !ref_box_pass(S, pinned(bo), pinned(t.d), f2i(T1.w))) continue;  // invisible to the reference
+      if ((ANY || t.careful) && !ref_box_pass(S, pinned(box_origin()), pinned(t.d), f2i(T1.w))) continue;  // invisible to the reference
       t.tbest = ANY ? t.tbest : tt;
       t.rbest = rank;
       t.sbest = first + k;
@@ -286,7 +289,7 @@ RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int
   Trav t;
   trav_init(t, o, d, stack);
   do {
-    while (!trav_step<ANY>(S, t, stack, bo)) {}
+    while (!trav_step<ANY>(S, t, stack, [&] { return bo; })) {}
   } while (!ANY && closest_needs_rerun(S, t, stack));
   best_t = t.tbest;
   best_slot = t.sbest;

@@ -329,7 +329,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
       age = 0;
       continue;
     }
-    if (have && t.node != kSentinel) trav_step<Job::kAny>(job.S, t, stack, job.box_origin(q, t));
+    if (have && t.node != kSentinel) trav_step<Job::kAny>(job.S, t, stack, [&] { return job.box_origin(q, t); });
   }
 #ifdef RTP_TRACE_TIMING
   if (lane == 0) {
