@@ -146,3 +146,30 @@ def has_cuda():
         return torch.cuda.is_available()
     except Exception:
         return False
+
+
+def soup(po, seed, n_tris=160):
+    """Triangle soup built to produce ties: vertices snapped to a coarse grid (coplanar faces, shared edges and
+    vertices that rays hit exactly), exact duplicates of faces, zero-area faces; several BoundingBoxes."""
+    rng = np.random.default_rng(seed)
+    grid = rng.integers(-4, 5, (n_tris // 2, 3)).astype(np.float32) / 4
+    verts = np.concatenate([grid, rng.uniform(-1, 1, (n_tris // 2, 3)).astype(np.float32)])
+    verts = np.concatenate([verts, np.ones((len(verts), 1), np.float32)], 1)
+    faces = rng.integers(0, len(verts), (n_tris, 3)).astype(np.int32)
+    faces[: n_tris // 3] = rng.integers(0, len(grid), (n_tris // 3, 3))          # grid-only faces
+    faces[n_tris // 3: n_tris // 3 + 12] = faces[:12]                              # duplicates (equal t: first visited wins)
+    faces[-6:, 2] = faces[-6:, 1]                                                   # degenerate
+    # every face has a material: faces without one (-1) shade with whatever the previous hit left in the reference's
+    # member variables (SURVEY.md Q4) - order-dependent there, the documented deviation of the product
+    face_mat = rng.integers(0, 2, n_tris).astype(np.int32)
+    mats = np.array([[0.1, 0.1, 0.1, 0.6, 0.3, 0.2, 0.9, 0.9, 0.9, 20, 1, 1],
+                     [0.0, 0.1, 0.2, 0.2, 0.5, 0.7, 0.3, 0.3, 0.3, 3, 1, 1]], np.float32)
+    m = po.Mesh(verts, None, faces, face_mat, mats)
+    return m.build_boxes(min_faces=24)
+
+
+SOUP_VIEWS = [None,                                                     # default camera: axis-aligned central rays
+              np.array([1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, -1.5], np.float32),
+              np.array([0, 0, 1, 0.25, 0, 1, 0, -0.25, -1, 0, 0, -2], np.float32)]
+SOUP_LIGHTS = np.array([[-0.5, 2, 3, 1, 1, 1], [1.5, -1, 2, 0.5, 0.4, 0.3]], np.float32)
+SOUP_DIRL = np.array([[0.2, -1.0, 0.1, 0.3, 0.3, 0.3]], np.float32)

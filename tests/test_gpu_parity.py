@@ -8,7 +8,7 @@ face ids and primary t bit-identical on every pixel, RGB within 1/255 on every n
 import numpy as np
 import pytest
 
-from conftest import bits_equal, golden_cases, load_case, load_golden_mesh
+from conftest import bits_equal, golden_cases, load_case, load_golden_mesh, soup, SOUP_VIEWS, SOUP_LIGHTS, SOUP_DIRL
 
 pytestmark = pytest.mark.gpu
 TOL = 1.0 / 255.0
@@ -213,3 +213,21 @@ def test_error_paths(rtp):
     bad[0, 0] = 99
     with pytest.raises(rtp.RtpError):
         rtp.Scene(m.verts, m.normals, bad, m.face_mat, m.materials, m.shape)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_tie_heavy_random_scenes_match_the_oracle(rtp, po, seed):
+    """The fuzz of tests/test_hostsim.py on the device: triangle soups with coplanar, duplicated and degenerate
+    faces seen along grid-aligned rays - primary ids identical, RGB within 1/255 (bit-equal except powf)."""
+    m = soup(po, seed, n_tris=400)
+    s = make_scene(rtp, m, with_boxes=True)
+    s.set_lights(SOUP_LIGHTS, SOUP_DIRL)
+    for view in SOUP_VIEWS:
+        s.set_camera(72, 56, view)
+        out = s.render(72, 56, max_depth=3)
+        o = po.render(m, 72, 56, view=view, max_depth=3, point_lights=SOUP_LIGHTS, dir_lights=SOUP_DIRL)
+        check_image(out["rgb"].reshape(-1, 3), out["hit"].ravel(), o["rgb"], o["hit"], exact_fraction=0.5)
+        st = out["stats"]
+        assert [st["rays_primary"], st["rays_shadow"], st["rays_reflection"], st["hits"]] == \
+               [o["counts"][k] for k in ("primary", "shadow", "reflection", "hits")]
+    s.close()
