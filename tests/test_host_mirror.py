@@ -274,3 +274,59 @@ def test_png_writer_roundtrip(w, h, tmp_path):
     out = str(tmp_path / "o.png")
     assert subprocess.run([CLI, "--size", str(w), str(h), "--png-from-u8", str(tmp_path / "in.u8"), out]).returncode == 0
     assert np.array_equal(read_png_rgb8(out), px)
+
+
+def random_obj_text(seed):
+    """OBJ text with the spellings a parser can trip over: mixed separators and line ends, signs, exponents, vertex
+    colours, v/t/n face tokens, polygons, comments, unknown keywords, material switches (some unknown)."""
+    rng = np.random.default_rng(seed)
+    nv = int(rng.integers(8, 60))
+    eol = lambda: "\r\n" if rng.random() < 0.3 else "\n"
+    sep = lambda: rng.choice([" ", "  ", "\t", " \t "])
+    def num():
+        x = float(rng.normal()) * 10.0 ** int(rng.integers(-3, 4))
+        return rng.choice([f"{x:.6g}", f"{x:+.4f}", f"{x:.3e}", f"{x:.2E}", str(int(x)), f"{x:.1f}".lstrip("0") or "0"])
+    out = ["# generated" + eol(), "mtllib quirks.mtl" + eol()]
+    with_vn = rng.random() < 0.5
+    for _ in range(nv):
+        line = "v " + sep().join(num() for _ in range(3))
+        if rng.random() < 0.2:
+            line += sep() + sep().join(f"{rng.random():.3f}" for _ in range(3))
+        out.append(line + eol())
+        if rng.random() < 0.05:
+            out.append(rng.choice(["# note", "g group1", "s off", "vt 0.5 0.5", "o thing", ""]) + eol())
+    if with_vn:
+        for _ in range(nv if rng.random() < 0.7 else nv - 1):
+            out.append("vn " + sep().join(num() for _ in range(3)) + eol())
+    for _ in range(int(rng.integers(10, 80))):
+        r = rng.random()
+        if r < 0.1:
+            out.append("usemtl " + rng.choice(["red", "blue", "nosuch", "green"]) + eol())
+            continue
+        k = 3 if r < 0.85 else int(rng.integers(4, 7))
+        ids = rng.integers(1, nv + 1, k)
+        form = rng.choice(["v", "v/t", "v//n", "v/t/n"])
+        tok = {"v": lambda i: f"{i}", "v/t": lambda i: f"{i}/{i}", "v//n": lambda i: f"{i}//{i}", "v/t/n": lambda i: f"{i}/{i}/{i}"}[form]
+        out.append("f " + sep().join(tok(int(i)) for i in ids) + (sep() if rng.random() < 0.2 else "") + eol())
+    text = "".join(out)
+    return text.rstrip("\r\n") if rng.random() < 0.3 else text
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_parallel_obj_ingest_fuzz(seed, tmp_path):
+    need_cli()
+    path = str(tmp_path / "fuzz.obj")
+    open(path, "w", newline="").write(random_obj_text(seed))
+    open(str(tmp_path / "quirks.mtl"), "w").write(open(os.path.join(GOLDEN, "quirks.mtl")).read())
+    ref = str(tmp_path / "serial")
+    r = subprocess.run([CLI, "--model", path, "--dump-scene", ref, "--serial-obj"], capture_output=True, text=True)
+    if r.returncode != 0:
+        pytest.skip("no faces in this file")
+    for threads, chunk in ((4, 32), (8, 7)):
+        pre = str(tmp_path / f"par{threads}")
+        env = dict(os.environ, RTP_OBJ_THREADS=str(threads), RTP_OBJ_MIN_CHUNK=str(chunk))
+        r2 = subprocess.run([CLI, "--model", path, "--dump-scene", pre], capture_output=True, text=True, env=env)
+        assert r2.returncode == 0, r2.stderr
+        for suffix in DUMPS:
+            a, b = np.fromfile(f"{ref}.{suffix}", np.uint32), np.fromfile(f"{pre}.{suffix}", np.uint32)
+            assert np.array_equal(a, b), f"seed {seed}: {suffix} differs ({threads} threads)"
