@@ -686,6 +686,7 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
   cfg.blocks_coop = sms * 2;
+  if (const char *e = std::getenv("RTP_COOP_BLOCKS")) cfg.blocks_coop = sms * std::max(1, std::atoi(e));  // per SM (tuning runs)
 }
 
 void launch_peer_barrier(unsigned *counter, unsigned target, unsigned long long timeout_ns, int *timeouts, cudaStream_t st) {
