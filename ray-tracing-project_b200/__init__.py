@@ -275,7 +275,7 @@ class Scene:
         self._check(self._L.rtp_render_wait(self._h, C.byref(st)))
         return st.as_dict()
 
-    def peer_barrier(self, d_counter, target, timeout_ms=2000, stream=None):
+    def peer_barrier(self, d_counter, target, timeout_ms=10000, stream=None):
         """rtp_peer_barrier: arrive at and wait on a counter in (peer) device memory, enqueued on `stream`."""
         self._check(self._L.rtp_peer_barrier(self._h, d_counter, int(target) & 0xffffffff, int(timeout_ms), stream))
 

@@ -74,6 +74,8 @@ class PeerImage:
         self.frame = 0
         self.token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
         self.counter = self.base + 2 * self.stride  # uint32 in rank 0's memory, reached by every rank over NVLink
+        if world > 1:
+            dist.barrier()  # every rank has the block mapped before anybody's first frame arrives at the counter
 
     def planes(self, frame=None):
         """(rgb8 pointer, hit pointer or None) of the buffer frame `frame` is written to."""
@@ -95,7 +97,7 @@ class PeerImage:
             self.base = None
 
 
-def render_frame_peer(scene, img, max_depth, stream, flags=0, barrier="peer", timeout_ms=2000):
+def render_frame_peer(scene, img, max_depth, stream, flags=0, barrier="peer", timeout_ms=10000):
     """One frame: every rank renders its tiles and resolves them straight into rank 0's image (peer stores over
     NVLink), then arrives at the frame barrier.  barrier = "peer": the library's own one-thread kernel
     (rtp_peer_barrier: system-scope atomic + wait on a counter in rank 0's memory; no collective left on this route);
