@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 5
+#define RTP_ABI_VERSION 6
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -110,6 +110,20 @@ typedef struct rtp_stats {
 int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out);
 int rtp_scene_destroy(rtp_scene *s); /* ~Flyscene / BoundingBox::deconstruct */
 
+/* The same scene on n_devices GPUs of one box, driven from ONE process: replaces the fan-out of the frame over
+ * Flyscene::THREADS row-band threads and their join inside raytraceScene (flyscene.cpp:266-289).  The mesh is
+ * flattened and its hierarchy built once, then replicated device to device; rtp_set_lights / rtp_set_camera reach
+ * every replica; rtp_render cuts the frame into interleaved 32x32 screen tiles (owner = (tx + ty) % n_devices), each
+ * device renders its tiles on its own stream, fed by its own host thread, and its resolve kernel stores the finished
+ * pixels straight into devices[0]'s image over NVLink (peer access); fork and join are CUDA events, then one copy to
+ * the host.  The image is bitwise the one a single device renders.  devices[] may name a device more than once (the
+ * ranks then share that GPU: how the sharded path is exercised on a one-GPU box).  rtp_render_async, the *_device
+ * entry points and rtp_trace_rays use devices[0] only. */
+#define RTP_MAX_DEVICES 64
+int rtp_scene_create_multi(const rtp_mesh *mesh, const int *devices, int n_devices, rtp_scene **out);
+int rtp_scene_device_count(const rtp_scene *s); /* 1 for rtp_scene_create */
+int rtp_device_count(void);                     /* CUDA devices visible to the process; negative rtp_status on error */
+
 /* Flyscene::lights, dirLights (public members, flyscene.hpp:132,135). */
 int rtp_set_lights(rtp_scene *s, const rtp_lights *l);
 /* getCamera()->setViewport / setPerspectiveMatrix / view matrix (flyscene.cpp:14-15). */
@@ -128,8 +142,11 @@ int rtp_get_tile_groups(const rtp_scene *s); /* bands the most recently enqueued
  *   rgb   W*H*3 float  pixel_data[j][i] (row-major)
  *   rgb8  W*H*3 uint8  the values writePPMImage prints: min(255,(int)(255*c)) (ppmIO.hpp:150)
  *   hit   W*H   int32  primary-hit face id, -1 = background
- * With world > 1 only this rank's tiles are rendered; pixels of other ranks are left
- * untouched in the host buffers (use the *_device entry points + a gather for full frames). */
+ * With world > 1 (one virtual rank of a sharded frame, scenes of rtp_scene_create only: tests and external
+ * multi-process drivers) only this rank's tiles are rendered and copied; pixels of other ranks are left untouched in
+ * the host buffers.  A scene of rtp_scene_create_multi shards the frame itself: world must be 1.
+ * Limit: pixels per call x max(lights, 1) < 2^31 (shadow rays of a level are indexed in 32 bits) - RTP_ERR_INVALID
+ * otherwise.  The camera may be arbitrarily far from the scene: the hierarchy's padding follows ulp(|eye|). */
 int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8, int32_t *hit,
                rtp_stats *st);
 
@@ -186,9 +203,15 @@ int rtp_shared_free(int device, void *d_ptr, int opened /* 1: came from rtp_shar
  * system-scope atomic over NVLink and waits until it has reached `target` (= world x frame number, frames counted
  * from 1; the counter is never reset).  Work enqueued behind it on GPU 0 sees every rank's pixels.  A wait that is not
  * satisfied within timeout_ms gives up (no hang) and is counted: rtp_peer_barrier_timeouts (synchronises the device)
- * returns how many did, or a negative rtp_status.  Replaces the join of raytraceScene's threads (flyscene.cpp:287-289). */
+ * returns how many did, or a negative rtp_status.  Replaces the join of raytraceScene's threads (flyscene.cpp:287-289).
+ * A timeout is STICKY: the counter stays short of the missing arrivals, so the frame it happened in is incomplete on
+ * GPU 0 and every later wait would spin for the full timeout.  The next rtp_peer_barrier / rtp_render_image_device on
+ * that scene therefore fails with RTP_ERR_STATE (the count lives in page-locked mapped memory: the check does not
+ * synchronise the device).  To go on, every rank re-creates / re-opens the shared block (fresh counter) and calls
+ * rtp_peer_barrier_reset. */
 int rtp_peer_barrier(rtp_scene *s, void *d_counter, uint32_t target, int timeout_ms, void *stream);
 int rtp_peer_barrier_timeouts(rtp_scene *s);
+int rtp_peer_barrier_reset(rtp_scene *s);
 
 /* ---- single-ray API ---------------------------------------------------------------------- */
 typedef enum rtp_ray_mode {

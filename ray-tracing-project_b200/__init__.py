@@ -62,7 +62,8 @@ EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_c
            "rtp_tile_buffer_bytes", "rtp_render_tiles_device", "rtp_untile_device", "rtp_trace_rays",
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
            "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_render_async", "rtp_render_wait", "rtp_peer_barrier", "rtp_peer_barrier_timeouts", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
-           "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free"]
+           "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free", "rtp_scene_create_multi", "rtp_scene_device_count",
+           "rtp_device_count", "rtp_peer_barrier_reset"]
 
 _lib = None
 
@@ -83,6 +84,10 @@ def lib():
         L.rtp_tile_buffer_bytes.restype = C.c_size_t
         L.rtp_tile_buffer_bytes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
         L.rtp_scene_create.argtypes = [C.POINTER(RtpMesh), C.c_int, C.POINTER(C.c_void_p)]
+        L.rtp_scene_create_multi.argtypes = [C.POINTER(RtpMesh), C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        L.rtp_scene_device_count.argtypes = [C.c_void_p]
+        L.rtp_device_count.argtypes = []
+        L.rtp_peer_barrier_reset.argtypes = [C.c_void_p]
         L.rtp_scene_destroy.argtypes = [C.c_void_p]
         L.rtp_set_lights.argtypes = [C.c_void_p, C.POINTER(RtpLights)]
         L.rtp_set_camera.argtypes = [C.c_void_p, C.POINTER(RtpCamera)]
@@ -185,16 +190,28 @@ def make_opts(w, h, max_depth=2, background=BACKGROUND, rank=0, world=1, flags=0
     return o
 
 
+def device_count():
+    n = lib().rtp_device_count()
+    if n < 0:
+        raise RtpError(f"rtp error {n}: {lib().rtp_last_error().decode(errors='replace')}")
+    return n
+
+
 class Scene:
-    """A scene on one CUDA device (rtp_scene handle)."""
+    """A scene on one CUDA device (rtp_scene handle), or - devices=[...] - replicated on several devices of the box
+    and driven from this one process (rtp_scene_create_multi: render() then shards the frame over them)."""
 
     def __init__(self, verts, normals, faces, face_mat, materials, shape, face_normal=None, boxes=None,
-                 box_off=None, box_faces=None, device=-1, min_faces=0, max_boxes=0, build=0):
+                 box_off=None, box_faces=None, device=-1, min_faces=0, max_boxes=0, build=0, devices=None):
         self._h = C.c_void_p()
         self._L = lib()
         m, keep = make_mesh_struct(verts, normals, faces, face_mat, materials, shape, face_normal, boxes,
                                    box_off, box_faces, min_faces, max_boxes, build)
-        self._check(self._L.rtp_scene_create(C.byref(m), device, C.byref(self._h)))
+        if devices is None:
+            self._check(self._L.rtp_scene_create(C.byref(m), device, C.byref(self._h)))
+        else:
+            arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+            self._check(self._L.rtp_scene_create_multi(C.byref(m), arr, len(devices), C.byref(self._h)))
         self.n_faces = m.n_faces
         del keep
 
@@ -278,6 +295,12 @@ class Scene:
     def peer_barrier(self, d_counter, target, timeout_ms=10000, stream=None):
         """rtp_peer_barrier: arrive at and wait on a counter in (peer) device memory, enqueued on `stream`."""
         self._check(self._L.rtp_peer_barrier(self._h, d_counter, int(target) & 0xffffffff, int(timeout_ms), stream))
+
+    def device_count(self):
+        return int(self._L.rtp_scene_device_count(self._h))
+
+    def peer_barrier_reset(self):
+        self._check(self._L.rtp_peer_barrier_reset(self._h))
 
     def peer_barrier_timeouts(self):
         n = self._L.rtp_peer_barrier_timeouts(self._h)

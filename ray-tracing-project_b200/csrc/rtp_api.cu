@@ -2,11 +2,20 @@
 // There is no CPU fallback here: every compute entry point needs a CUDA device.
 #include <cuda_runtime.h>
 
+#include <atomic>
+#include <cmath>
+#include <type_traits>
+#include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/rtp.h"
@@ -65,13 +74,68 @@ struct Frame {
   int n_px = 0, tiles_x = 0;
   DevBuf<float4> fb, ksdeep, direct, ray_o0, ray_o1, ray_d0, ray_d1;
   int n_lights = 0, n_valid = 0;
-  DevBuf<float4> pbuf, nbuf;
-  DevBuf<int> primface, hit_slot, hitlist, tile_ids, local_of_tile;
+  DevBuf<float4> pbuf, dbuf;
+  DevBuf<int> primface, hit_slot, hitq, tile_ids, local_of_tile;
   DevBuf<unsigned char> occl;
-  DevBuf<float> hit_t;
   DevBuf<float> out_rgb;
   DevBuf<unsigned char> out_rgb8;
   DevBuf<int> out_hit;
+  std::vector<int32_t> tiles_host;  // ids of the owned tiles (host copy of tile_ids)
+};
+
+// One host thread per extra GPU of a multi-device scene: the frame of device r is enqueued by worker r while the
+// caller's thread enqueues device 0's (a frame is a dozen launches; issued from one thread for 8 devices they would
+// start up to ~0.3 ms apart).  A worker spins for a short while after a job - a render loop finds it awake - then sleeps.
+class Worker {
+ public:
+  Worker() : th_([this] { run(); }) {}
+  ~Worker() {
+    { std::lock_guard<std::mutex> g(m_); quit_ = true; state_.store(1, std::memory_order_release); }
+    cv_.notify_one();
+    th_.join();
+  }
+  void submit(std::function<int()> fn) {
+    { std::lock_guard<std::mutex> g(m_); job_ = std::move(fn); state_.store(1, std::memory_order_release); }
+    cv_.notify_one();
+  }
+  int wait() {  // result of the submitted job
+    while (state_.load(std::memory_order_acquire) != 2) {
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+    state_.store(0, std::memory_order_release);
+    return rc_;
+  }
+
+ private:
+  void run() {
+    for (;;) {
+      const auto t0 = std::chrono::steady_clock::now();
+      while (state_.load(std::memory_order_acquire) != 1) {  // spin, then sleep
+        if (std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(300)) {
+          std::unique_lock<std::mutex> lk(m_);
+          cv_.wait(lk, [this] { return state_.load(std::memory_order_acquire) == 1; });
+          break;
+        }
+      }
+      std::function<int()> fn;
+      {
+        std::lock_guard<std::mutex> g(m_);
+        if (quit_) return;
+        fn.swap(job_);
+      }
+      rc_ = fn ? fn() : 0;
+      state_.store(2, std::memory_order_release);
+    }
+  }
+  std::mutex m_;
+  std::condition_variable cv_;
+  std::function<int()> job_;
+  std::atomic<int> state_{0};  // 0 idle, 1 job posted, 2 job done
+  bool quit_ = false;
+  int rc_ = 0;
+  std::thread th_;  // last member: the thread starts when everything above exists
 };
 
 }  // namespace
@@ -83,7 +147,17 @@ struct rtp_scene {
   DevBuf<int> face_of;
   DevBuf<int> counters;
   DevBuf<int> park;  // parked-ray list of the trace kernels
-  DevBuf<int> barrier_timeouts;  // [1] waits of rtp_peer_barrier that gave up
+  int *barrier_timeouts = nullptr;      // [1] waits of rtp_peer_barrier that gave up: page-locked, mapped - the kernel
+  int *barrier_timeouts_dev = nullptr;  // writes it through the device alias, the host reads it without a device sync
+  float pad_cur = 0.f;  // padding of the hierarchy's boxes right now (build-time pad, grown by ensure_pad)
+  // multi-device scene (rtp_scene_create_multi): this is device 0's scene, peers[r - 1] the replica of rank r
+  std::vector<rtp_scene *> peers;
+  std::vector<std::unique_ptr<Worker>> workers;  // one per peer
+  rtp_scene *primary = nullptr;                  // set in a replica
+  cudaEvent_t frame_start = nullptr, frame_done = nullptr;  // cross-device fork / join of a multi-device frame
+  std::string err;                               // error text of a job that ran on a worker thread
+  int *staging = nullptr;                        // page-locked host staging (world > 1 renders, ray batches)
+  size_t staging_bytes = 0;
   DeviceScene dS;
   std::vector<float4> lights_host;  // what s->lights holds
   DeviceCamera cam;
@@ -153,113 +227,100 @@ extern "C" {
 const char *rtp_last_error(void) { return g_err.c_str(); }
 int rtp_abi_version(void) { return RTP_ABI_VERSION; }
 
-int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
-  if (!mesh || !out) return fail(RTP_ERR_INVALID, "rtp_scene_create: null argument");
-  *out = nullptr;
-  int ndev = 0;
-  cudaError_t e = cudaGetDeviceCount(&ndev);
-  if (e != cudaSuccess || ndev == 0)
-    return fail(RTP_ERR_CUDA, std::string("rtp_scene_create: no CUDA device (") +
-                                  (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
-                                  "); this library has no CPU fallback");
-  if (device < 0) CK(cudaGetDevice(&device));
-  if (device >= ndev) return fail(RTP_ERR_INVALID, "rtp_scene_create: device ordinal out of range");
-  rtp_scene *s = new (std::nothrow) rtp_scene();
-  if (!s) return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory");
-  s->device = device;
-  // where the traversal hierarchy is built: rtp_mesh.build, overridden by RTP_BVH_BUILD=gpu|host
-  bool gpu_build = mesh->build == RTP_BUILD_GPU_LBVH;
-  if (const char *be = std::getenv("RTP_BVH_BUILD")) gpu_build = std::string(be) == "gpu";
-  if (mesh->n_faces < 64) gpu_build = false;  // tiny scenes: nothing to gain
-  std::string msg;
-  try {
-    msg = flatten_scene(*mesh, s->host, 0, !gpu_build);
-  } catch (const std::bad_alloc &) {
-    delete s;
-    return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory while flattening");
-  }
-  if (!msg.empty()) {
-    delete s;
-    return fail(RTP_ERR_INVALID, msg);
-  }
-  DeviceGuard g(device);
-  if (!g.ok) { delete s; return fail(RTP_ERR_CUDA, "rtp_scene_create: cudaSetDevice failed"); }
-  auto cleanup = [&](cudaError_t err, const char *what) {
-    std::string m = std::string(what) + ": " + cudaGetErrorString(err);
-    delete s;
-    return fail(RTP_ERR_CUDA, m);
-  };
-  if ((e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking)) != cudaSuccess) return cleanup(e, "cudaStreamCreate");
-  for (auto &ev : s->ev)
-    if ((e = cudaEventCreate(&ev)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
-  for (int i = 1; i < kMaxGroups; ++i)
-    if ((e = cudaStreamCreateWithFlags(&s->gstream[i], cudaStreamNonBlocking)) != cudaSuccess) return cleanup(e, "cudaStreamCreate");
-  if ((e = cudaEventCreateWithFlags(&s->gfork, cudaEventDisableTiming)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
-  for (int i = 1; i < kMaxGroups; ++i)
-    if ((e = cudaEventCreateWithFlags(&s->gjoin[i], cudaEventDisableTiming)) != cudaSuccess) return cleanup(e, "cudaEventCreate");
+}  // extern "C"
+
+namespace {
+
+// streams, events, tuning knobs of one device's scene (the device is current)
+int init_device_side(rtp_scene *s) {
+  CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+  for (auto &ev : s->ev) CK(cudaEventCreate(&ev));
+  for (int i = 1; i < kMaxGroups; ++i) CK(cudaStreamCreateWithFlags(&s->gstream[i], cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&s->gfork, cudaEventDisableTiming));
+  for (int i = 1; i < kMaxGroups; ++i) CK(cudaEventCreateWithFlags(&s->gjoin[i], cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&s->frame_start, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&s->frame_done, cudaEventDisableTiming));
   if (const char *te = std::getenv("RTP_TIMELINE")) s->timeline = std::atoi(te);
   if (const char *ge = std::getenv("RTP_GROUPS")) s->groups = std::min(std::max(std::atoi(ge), 0), kMaxGroups);
-  HostScene &h = s->host;
+  return RTP_OK;
+}
+
+// the flattened scene of h (host arrays) -> device arrays of s; with gpu_build the hierarchy is built there
+int upload_scene(rtp_scene *s, HostScene &h, bool gpu_build) {
   if (gpu_build) {
     // rank-ordered triangles go up once; the device sorts them, builds the hierarchy and permutes
     DevBuf<float4> tris_in, vnorm_in;
     DevBuf<int> face_in;
     const size_t n = (size_t)h.n_tris;
-    if ((e = tris_in.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
-    if ((e = vnorm_in.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
-    if ((e = face_in.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face ids");
-    if ((e = s->tris.ensure(4 * n)) != cudaSuccess) return cleanup(e, "alloc tris");
-    if ((e = s->vnorm.ensure(3 * n)) != cudaSuccess) return cleanup(e, "alloc vnorm");
-    if ((e = s->face_of.ensure(n)) != cudaSuccess) return cleanup(e, "alloc face_of");
-    if ((e = s->nodes.ensure(4 * n)) != cudaSuccess) return cleanup(e, "alloc nodes");
+    CK(tris_in.upload(h.tris, s->stream));
+    CK(vnorm_in.upload(h.vnorm, s->stream));
+    CK(face_in.upload(h.face_of, s->stream));
+    CK(s->tris.ensure(4 * n));
+    CK(s->vnorm.ensure(3 * n));
+    CK(s->face_of.ensure(n));
+    CK(s->nodes.ensure(4 * n));
     int n_nodes = 0, height = 0;
-    e = build_lbvh_device(tris_in.p, vnorm_in.p, face_in.p, h.n_tris, h.pad, h.scene_lo, h.scene_hi, 4, s->tris.p, s->vnorm.p,
-                          s->face_of.p, s->nodes.p, &n_nodes, &height, s->stream);
-    if (e != cudaSuccess) return cleanup(e, "build_lbvh_device");
-    if (height >= kStackSize - 2) {
-      delete s;
+    CK(build_lbvh_device(tris_in.p, vnorm_in.p, face_in.p, h.n_tris, h.pad, h.scene_lo, h.scene_hi, 4, s->tris.p, s->vnorm.p,
+                         s->face_of.p, s->nodes.p, &n_nodes, &height, s->stream));
+    if (height >= kStackSize - 2)
       return fail(RTP_ERR_INVALID, "device-built BVH is deeper than the traversal stack; use RTP_BUILD_HOST_SAH");
-    }
     h.n_nodes = n_nodes;
     h.bvh_depth = height;
   } else {
-    if ((e = s->nodes.upload(h.nodes, s->stream)) != cudaSuccess) return cleanup(e, "upload nodes");
-    if ((e = s->tris.upload(h.tris, s->stream)) != cudaSuccess) return cleanup(e, "upload tris");
-    if ((e = s->vnorm.upload(h.vnorm, s->stream)) != cudaSuccess) return cleanup(e, "upload vnorm");
-    if ((e = s->face_of.upload(h.face_of, s->stream)) != cudaSuccess) return cleanup(e, "upload face_of");
+    CK(s->nodes.upload(h.nodes, s->stream));
+    CK(s->tris.upload(h.tris, s->stream));
+    CK(s->vnorm.upload(h.vnorm, s->stream));
+    CK(s->face_of.upload(h.face_of, s->stream));
   }
-  if ((e = s->boxes.upload(h.boxes, s->stream)) != cudaSuccess) return cleanup(e, "upload boxes");
-  if ((e = s->materials.upload(h.materials, s->stream)) != cudaSuccess) return cleanup(e, "upload materials");
-  if ((e = s->counters.ensure(kCtrInts * kMaxGroups)) != cudaSuccess) return cleanup(e, "alloc counters");
-  if ((e = cudaMemsetAsync(s->counters.p, 0, kCtrInts * kMaxGroups * sizeof(int), s->stream)) != cudaSuccess) return cleanup(e, "zero counters");
-  if ((e = cudaStreamSynchronize(s->stream)) != cudaSuccess) return cleanup(e, "upload sync");
-  // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
-  BigVec<float4>().swap(h.nodes);
-  BigVec<float4>().swap(h.tris);
-  BigVec<float4>().swap(h.vnorm);
+  CK(s->boxes.upload(h.boxes, s->stream));
+  CK(s->materials.upload(h.materials, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return RTP_OK;
+}
+
+// device arrays of src (another device, or the same one) -> device arrays of dst: the hierarchy is built once
+int replicate_scene(rtp_scene *dst, const rtp_scene *src) {
+  auto copy = [&](auto &d, const auto &sbuf) -> cudaError_t {
+    cudaError_t e = d.ensure(sbuf.n);
+    if (e != cudaSuccess || sbuf.n == 0) return e;
+    using T = typename std::remove_reference<decltype(*d.p)>::type;
+    return cudaMemcpyPeerAsync(d.p, dst->device, sbuf.p, src->device, sbuf.n * sizeof(T), dst->stream);
+  };
+  CK(copy(dst->nodes, src->nodes));
+  CK(copy(dst->tris, src->tris));
+  CK(copy(dst->vnorm, src->vnorm));
+  CK(copy(dst->face_of, src->face_of));
+  CK(copy(dst->boxes, src->boxes));
+  CK(copy(dst->materials, src->materials));
+  CK(cudaStreamSynchronize(dst->stream));
+  return RTP_OK;
+}
+
+// counters, parked-ray list, DeviceScene view, launch configuration (h: scalar description of the scene)
+int finish_scene(rtp_scene *s, const HostScene &h) {
+  CK(s->counters.ensure(kCtrInts * kMaxGroups));
+  CK(cudaMemsetAsync(s->counters.p, 0, kCtrInts * kMaxGroups * sizeof(int), s->stream));
   DeviceScene &d = s->dS;
   d.nodes = s->nodes.p; d.tris = s->tris.p; d.vnorm = s->vnorm.p; d.boxes = s->boxes.p;
   d.face_of = s->face_of.p; d.materials = s->materials.p; d.lights = nullptr; d.n_lights = 0;
   std::memcpy(d.minv, h.minv, sizeof d.minv);
   d.n_tris = h.n_tris; d.n_nodes = h.n_nodes; d.n_boxes = h.n_boxes;
-  query_launch_cfg(device, s->cfg);
+  s->pad_cur = h.pad;
+  query_launch_cfg(s->device, s->cfg);
   constexpr int kParkCap = 1 << 17;  // 131072 parked rays (36 MiB); a full list only means no more parking
-  if ((e = s->park.ensure((size_t)kParkCap * kParkSlotBytes / sizeof(int))) != cudaSuccess) return cleanup(e, "alloc parked-ray list");
+  CK(s->park.ensure((size_t)kParkCap * kParkSlotBytes / sizeof(int)));
   s->cfg.park_slots = s->park.p;
   s->cfg.park_cap = kParkCap;
-  {
-    int l2 = 0;
-    cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, device);
-    const size_t scene_bytes = ((size_t)h.n_nodes + (size_t)h.n_tris) * 64;
-    s->cfg.scene_exceeds_l2 = scene_bytes > (size_t)(l2 > 0 ? l2 : (64 << 20)) / 2;
-  }
-  if ((e = cudaGetLastError()) != cudaSuccess) return cleanup(e, "query_launch_cfg");
-  *out = s;
+  int l2 = 0;
+  cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, s->device);
+  const size_t scene_bytes = ((size_t)h.n_nodes + (size_t)h.n_tris) * 64;
+  s->cfg.scene_exceeds_l2 = scene_bytes > (size_t)(l2 > 0 ? l2 : (64 << 20)) / 2;
+  CK(cudaStreamSynchronize(s->stream));
+  CK(cudaGetLastError());
   return RTP_OK;
 }
 
-int rtp_scene_destroy(rtp_scene *s) {
-  if (!s) return RTP_OK;
+void destroy_one(rtp_scene *s) {
   DeviceGuard g(s->device);
   if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
   for (auto &ev : s->ev)
@@ -271,11 +332,15 @@ int rtp_scene_destroy(rtp_scene *s) {
     if (s->gjoin[i]) cudaEventDestroy(s->gjoin[i]);
   }
   if (s->gfork) cudaEventDestroy(s->gfork);
+  if (s->frame_start) cudaEventDestroy(s->frame_start);
+  if (s->frame_done) cudaEventDestroy(s->frame_done);
   for (int i = 0; i < kMaxGroups; ++i) {
     if (s->cstream[i]) { cudaStreamSynchronize(s->cstream[i]); cudaStreamDestroy(s->cstream[i]); }
     if (s->resolved[i]) cudaEventDestroy(s->resolved[i]);
   }
   if (s->counters_pinned) cudaFreeHost(s->counters_pinned);
+  if (s->barrier_timeouts) cudaFreeHost(s->barrier_timeouts);
+  if (s->staging) cudaFreeHost(s->staging);
   for (auto &a : s->aslot) {
     if (a.counters_host) cudaFreeHost(a.counters_host);
     if (a.ev0) cudaEventDestroy(a.ev0);
@@ -284,16 +349,133 @@ int rtp_scene_destroy(rtp_scene *s) {
       if (e) cudaEventDestroy(e);
   }
   delete s;  // DevBuf destructors free device memory while the device is current
+}
+
+void destroy_set(rtp_scene *s) {
+  s->workers.clear();  // joins the worker threads
+  for (rtp_scene *p : s->peers) destroy_one(p);
+  s->peers.clear();
+  destroy_one(s);
+}
+
+// The scalar part of a HostScene (no arrays): what a replica needs to describe itself.
+void copy_meta(HostScene &dst, const HostScene &src) {
+  std::memcpy(dst.minv, src.minv, sizeof dst.minv);
+  dst.n_tris = src.n_tris; dst.n_nodes = src.n_nodes; dst.n_boxes = src.n_boxes; dst.bvh_depth = src.bvh_depth;
+  dst.n_flagged = src.n_flagged; dst.n_degenerate = src.n_degenerate; dst.pad = src.pad; dst.maxabs = src.maxabs;
+  std::memcpy(dst.scene_lo, src.scene_lo, sizeof dst.scene_lo);
+  std::memcpy(dst.scene_hi, src.scene_hi, sizeof dst.scene_hi);
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtp_scene_create_multi(const rtp_mesh *mesh, const int *devices, int n_devices, rtp_scene **out) {
+  if (!mesh || !out || !devices || n_devices < 1 || n_devices > RTP_MAX_DEVICES)
+    return fail(RTP_ERR_INVALID, "rtp_scene_create_multi: null argument or n_devices outside [1, RTP_MAX_DEVICES]");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(RTP_ERR_CUDA, std::string("rtp_scene_create: no CUDA device (") +
+                                  (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                                  "); this library has no CPU fallback");
+  std::vector<int> dev(devices, devices + n_devices);
+  for (int &d : dev) {
+    if (d < 0) CK(cudaGetDevice(&d));
+    if (d >= ndev) return fail(RTP_ERR_INVALID, "rtp_scene_create: device ordinal out of range");
+  }
+  rtp_scene *s = new (std::nothrow) rtp_scene();
+  if (!s) return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory");
+  s->device = dev[0];
+  // where the traversal hierarchy is built: rtp_mesh.build, overridden by RTP_BVH_BUILD=gpu|host
+  bool gpu_build = mesh->build == RTP_BUILD_GPU_LBVH;
+  if (const char *be = std::getenv("RTP_BVH_BUILD")) gpu_build = std::string(be) == "gpu";
+  if (mesh->n_faces < 64) gpu_build = false;  // tiny scenes: nothing to gain
+  std::string msg;
+  try {
+    msg = flatten_scene(*mesh, s->host, 0, !gpu_build);  // ONCE, whatever the number of devices
+  } catch (const std::bad_alloc &) {
+    delete s;
+    return fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory while flattening");
+  }
+  if (!msg.empty()) {
+    delete s;
+    return fail(RTP_ERR_INVALID, msg);
+  }
+  HostScene &h = s->host;
+  int rc = RTP_OK;
+  {
+    DeviceGuard g(dev[0]);
+    if (!g.ok) { delete s; return fail(RTP_ERR_CUDA, "rtp_scene_create: cudaSetDevice failed"); }
+    rc = init_device_side(s);
+    if (!rc) rc = upload_scene(s, h, gpu_build);
+    if (!rc) rc = finish_scene(s, h);
+  }
+  // the big flattened arrays now live on the device; keep only the BoundingBox view on the host
+  BigVec<float4>().swap(h.nodes);
+  BigVec<float4>().swap(h.tris);
+  BigVec<float4>().swap(h.vnorm);
+  for (int r = 1; r < n_devices && !rc; ++r) {
+    rtp_scene *p = new (std::nothrow) rtp_scene();
+    if (!p) { rc = fail(RTP_ERR_NOMEM, "rtp_scene_create: out of host memory"); break; }
+    p->device = dev[(size_t)r];
+    p->primary = s;
+    copy_meta(p->host, h);
+    s->peers.push_back(p);
+    DeviceGuard g(p->device);
+    if (!g.ok) { rc = fail(RTP_ERR_CUDA, "rtp_scene_create: cudaSetDevice failed"); break; }
+    if (p->device != s->device) {  // this device's kernels store their pixels into device 0's image
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, p->device, s->device);
+      if (!can) { rc = fail(RTP_ERR_CUDA, "rtp_scene_create_multi: device " + std::to_string(p->device) + " has no peer access to device " + std::to_string(s->device)); break; }
+      cudaError_t pe = cudaDeviceEnablePeerAccess(s->device, 0);
+      if (pe == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+      else if (pe != cudaSuccess) { rc = fail(RTP_ERR_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(pe)); break; }
+    }
+    rc = init_device_side(p);
+    if (!rc) rc = replicate_scene(p, s);
+    if (!rc) rc = finish_scene(p, h);
+  }
+  if (!rc)
+    for (size_t r = 0; r < s->peers.size(); ++r) s->workers.emplace_back(new Worker());
+  if (rc) {
+    const std::string keep = g_err;
+    destroy_set(s);
+    g_err = keep;
+    return rc;
+  }
+  *out = s;
   return RTP_OK;
 }
 
-int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
-  if (!s || !l) return fail(RTP_ERR_INVALID, "rtp_set_lights: null argument");
-  if (l->n_point < 0 || l->n_dir < 0 || (l->n_point && !l->point) || (l->n_dir && !l->dir))
-    return fail(RTP_ERR_INVALID, "rtp_set_lights: bad light arrays");
+int rtp_scene_create(const rtp_mesh *mesh, int device, rtp_scene **out) {
+  if (!mesh || !out) return fail(RTP_ERR_INVALID, "rtp_scene_create: null argument");
+  return rtp_scene_create_multi(mesh, &device, 1, out);
+}
+
+int rtp_scene_device_count(const rtp_scene *s) { return s ? 1 + (int)s->peers.size() : 0; }
+
+int rtp_device_count(void) {
+  int n = 0;
+  CK(cudaGetDeviceCount(&n));
+  return n;
+}
+
+int rtp_scene_destroy(rtp_scene *s) {
+  if (!s) return RTP_OK;
+  if (s->primary) return fail(RTP_ERR_INVALID, "rtp_scene_destroy: this handle is a replica owned by a multi-device scene");
+  destroy_set(s);
+  return RTP_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+int set_lights_one(rtp_scene *s, const rtp_lights *l, const std::vector<float4> &packed) {
   DeviceGuard g(s->device);
-  std::vector<float4> packed;
-  pack_lights(*l, packed);
   // unchanged light set (a render loop sets it before every frame): nothing to upload.  Otherwise the copy is
   // stream-ordered behind the previous frame (all its tile groups are joined into s->stream) and does not block
   // the host: frames of rtp_render_async stay in flight.  A re-allocation (more lights than ever before) waits.
@@ -310,9 +492,42 @@ int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
   return RTP_OK;
 }
 
+// The hierarchy's boxes are padded for the rounding of P = o + t*d, which grows with |o| (ulp(|o| + t)): a ray that
+// starts `dist` away from the origin needs a pad of ~8 ulp(dist).  The build-time pad (3e-5 x scene size) covers
+// origins up to ~30 scene sizes away; beyond that the boxes are widened in place, once, to what this origin needs
+// (only ever grows: a wider pad is always correct, it only culls a little less).
+int ensure_pad(rtp_scene *s, float dist) {
+  const float need = 1.0e-6f * dist;
+  if (!(need > s->pad_cur)) return RTP_OK;
+  DeviceGuard g(s->device);
+  cudaStream_t st = s->has_last ? s->last_stream : s->stream;
+  launch_inflate_nodes(s->nodes.p, s->host.n_nodes, need - s->pad_cur, st);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(st));  // a rare, one-off event: the next frame may run on any stream
+  s->pad_cur = need;
+  return RTP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtp_set_lights(rtp_scene *s, const rtp_lights *l) {
+  if (!s || !l) return fail(RTP_ERR_INVALID, "rtp_set_lights: null argument");
+  if (l->n_point < 0 || l->n_dir < 0 || (l->n_point && !l->point) || (l->n_dir && !l->dir))
+    return fail(RTP_ERR_INVALID, "rtp_set_lights: bad light arrays");
+  std::vector<float4> packed;
+  pack_lights(*l, packed);
+  int rc = set_lights_one(s, l, packed);
+  for (rtp_scene *p : s->peers)
+    if (!rc) rc = set_lights_one(p, l, packed);
+  return rc;
+}
+
 int rtp_set_tile_groups(rtp_scene *s, int groups) {
   if (!s || groups < 0 || groups > kMaxGroups) return fail(RTP_ERR_INVALID, "rtp_set_tile_groups: groups must be in [0, 8]");
   s->groups = groups;
+  for (rtp_scene *p : s->peers) p->groups = groups;
   return RTP_OK;
 }
 
@@ -323,7 +538,14 @@ int rtp_set_camera(rtp_scene *s, const rtp_camera *c) {
   if (!(c->viewport[2] > 0.f) || !(c->viewport[3] > 0.f)) return fail(RTP_ERR_INVALID, "rtp_set_camera: empty viewport");
   derive_camera(*c, s->cam);
   s->have_camera = true;
-  return RTP_OK;
+  const float dist = std::max(std::fabs(s->cam.eye[0]), std::max(std::fabs(s->cam.eye[1]), std::fabs(s->cam.eye[2])));
+  int rc = std::isfinite(dist) ? ensure_pad(s, dist) : RTP_OK;
+  for (rtp_scene *p : s->peers) {
+    p->cam = s->cam;
+    p->have_camera = true;
+    if (!rc && std::isfinite(dist)) rc = ensure_pad(p, dist);
+  }
+  return rc;
 }
 
 int rtp_scene_box_count(const rtp_scene *s) { return s ? s->host.n_boxes : 0; }
@@ -371,6 +593,10 @@ int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int wo
   const bool same = f.width == width && f.height == height && f.rank == rank && f.world == world &&
                     f.max_depth >= max_depth && f.n_px == n_paths && f.n_lights >= n_lights;
   if (same) return RTP_OK;
+  // shadow rays are indexed (hit, light) in 32 bits (FrameAny::count, cursors): refuse what would overflow
+  if ((long long)n_paths * n_lights > 0x7fffffffll)
+    return fail(RTP_ERR_INVALID, "render: paths x lights exceeds 2^31 - 1 shadow rays per level (" + std::to_string(n_paths) +
+                                     " x " + std::to_string(n_lights) + "): render fewer pixels per call or use fewer lights");
   // the buffers below are about to be re-sized / re-filled: wait for the frame that may still use them
   if (s->has_last) CK(cudaStreamSynchronize(s->last_stream));
   f.width = width; f.height = height; f.rank = rank; f.world = world; f.max_depth = max_depth; f.n_px = n_paths;
@@ -380,8 +606,8 @@ int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int wo
   CK(f.ksdeep.ensure(n));
   CK(f.direct.ensure(n * (size_t)max_depth));
   CK(f.ray_o0.ensure(n)); CK(f.ray_o1.ensure(n)); CK(f.ray_d0.ensure(n)); CK(f.ray_d1.ensure(n));
-  CK(f.primface.ensure(n)); CK(f.hit_slot.ensure(n)); CK(f.hit_t.ensure(n));
-  CK(f.hitlist.ensure(n)); CK(f.pbuf.ensure(n)); CK(f.nbuf.ensure(n));
+  CK(f.primface.ensure(n)); CK(f.hit_slot.ensure(n));
+  CK(f.pbuf.ensure(n)); CK(f.dbuf.ensure(n)); CK(f.hitq.ensure(n));
   CK(f.occl.ensure(n * (size_t)n_lights));
   f.n_valid = n_paths;
   if (with_tiles) {
@@ -393,6 +619,7 @@ int ensure_frame(rtp_scene *s, Frame &f, int width, int height, int rank, int wo
       valid += (long long)std::min(kTileDim, width - x0) * std::min(kTileDim, height - y0);
     }
     f.n_valid = (int)valid;
+    f.tiles_host = tiles;
     CK(f.tile_ids.upload(tiles, s->stream));
     CK(f.local_of_tile.upload(local, s->stream));
     CK(cudaStreamSynchronize(s->stream));
@@ -409,12 +636,13 @@ void fill_params(rtp_scene *s, Frame &f, const rtp_render_opts &o, float4 *fb, F
   p.max_depth = o.max_depth;
   p.bg[0] = o.background[0]; p.bg[1] = o.background[1]; p.bg[2] = o.background[2];
   p.fb = fb;
+  p.img_rgb = nullptr;
   p.img_rgb8 = nullptr;
   p.img_hit = nullptr;
   p.primface = f.primface.p; p.ksdeep = f.ksdeep.p; p.direct = f.direct.p;
   p.ray_o[0] = f.ray_o0.p; p.ray_o[1] = f.ray_o1.p; p.ray_d[0] = f.ray_d0.p; p.ray_d[1] = f.ray_d1.p;
-  p.hit_t = f.hit_t.p; p.hit_slot = f.hit_slot.p;
-  p.hitlist = f.hitlist.p; p.pbuf = f.pbuf.p; p.nbuf = f.nbuf.p; p.occl = f.occl.p;
+  p.hit_slot = f.hit_slot.p;
+  p.pbuf = f.pbuf.p; p.dbuf = f.dbuf.p; p.hitq = f.hitq.p; p.occl = f.occl.p;
   p.counters = s->counters.p;
 }
 
@@ -454,11 +682,10 @@ FrameParams group_params(const FrameParams &p, int g, int t0, int t1) {
   q.ksdeep = p.ksdeep + base;
   q.direct = p.direct + base * (size_t)p.max_depth;  // [max_depth][group pixels]
   for (int i = 0; i < 2; ++i) { q.ray_o[i] = p.ray_o[i] + base; q.ray_d[i] = p.ray_d[i] + base; }
-  q.hit_t = p.hit_t + base;
   q.hit_slot = p.hit_slot + base;
-  q.hitlist = p.hitlist + base;
   q.pbuf = p.pbuf + base;
-  q.nbuf = p.nbuf + base;
+  q.dbuf = p.dbuf + base;
+  q.hitq = p.hitq + base;
   q.occl = p.occl + base * (size_t)std::max(p.S.n_lights, 1);
   q.counters = p.counters + g * kCtrInts;
   return q;
@@ -522,12 +749,13 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   }
   CK(stamp("start", 0, 0, st));
   // launches are issued phase by phase across the groups, so that the groups advance together
-  for (int g = 0; g < G; ++g) { CK(mark(2)); launch_raygen(gp[g], gs[g]); ++n; CK(stamp("raygen", g, 0, gs[g])); }
+  if (p.user_rays)  // caller-supplied rays go through the ray list; camera rays are generated inside the trace kernel
+    for (int g = 0; g < G; ++g) { CK(mark(2)); launch_raygen(gp[g], gs[g]); ++n; CK(stamp("raygen", g, 0, gs[g])); }
   for (int d = 0; d < p.max_depth; ++d) {
     for (int g = 0; g < G; ++g) { CK(mark(0)); n += launch_closest(gp[g], d, gc[g], gs[g]); CK(stamp("closest", g, d, gs[g])); }
-    for (int g = 0; g < G; ++g) { CK(mark(2)); launch_prep(gp[g], d, gs[g]); ++n; CK(stamp("prep", g, d, gs[g])); }
     for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit(gp[g], d, gc[g], gs[g]); CK(stamp("anyhit", g, d, gs[g])); }
-    for (int g = 0; g < G; ++g) { CK(mark(2)); launch_accum(gp[g], d, gs[g]); ++n; CK(stamp("accum", g, d, gs[g])); }
+    if (p.max_depth > 1)  // max_depth 1: the resolve kernel shades the only level itself
+      for (int g = 0; g < G; ++g) { CK(mark(2)); launch_accum(gp[g], d, gs[g]); ++n; CK(stamp("accum", g, d, gs[g])); }
   }
   for (int g = 0; g < G; ++g) {
     CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
@@ -672,6 +900,8 @@ int rtp_render_image_device(rtp_scene *s, const rtp_render_opts *o, void *d_rgb8
   int rc = check_render_args(s, o);
   if (rc) return rc;
   if (!d_rgb8 && !d_hit) return fail(RTP_ERR_INVALID, "rtp_render_image_device: no output plane");
+  if (s->barrier_timeouts && *(volatile int *)s->barrier_timeouts != 0)
+    return fail(RTP_ERR_STATE, "rtp_render_image_device: an earlier frame barrier timed out (see rtp_peer_barrier)");
   DeviceGuard g(s->device);
   cudaStream_t cs = (cudaStream_t)stream;
   const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
@@ -721,11 +951,20 @@ int rtp_peer_barrier(rtp_scene *s, void *d_counter, uint32_t target, int timeout
   if (!s || !d_counter || timeout_ms <= 0) return fail(RTP_ERR_INVALID, "rtp_peer_barrier: bad argument");
   if (((size_t)d_counter & 3) != 0) return fail(RTP_ERR_INVALID, "rtp_peer_barrier: counter must be 4-byte aligned");
   DeviceGuard g(s->device);
-  if (!s->barrier_timeouts.p) {
-    CK(s->barrier_timeouts.ensure(1));
-    CK(cudaMemset(s->barrier_timeouts.p, 0, sizeof(int)));
+  if (!s->barrier_timeouts) {
+    // page-locked and mapped: the barrier kernel counts a timeout through the device alias, the host sees it at the
+    // next call without synchronising the device
+    CK(cudaHostAlloc((void **)&s->barrier_timeouts, sizeof(int), cudaHostAllocMapped));
+    *s->barrier_timeouts = 0;
+    CK(cudaHostGetDevicePointer((void **)&s->barrier_timeouts_dev, s->barrier_timeouts, 0));
   }
-  launch_peer_barrier((unsigned *)d_counter, target, (unsigned long long)timeout_ms * 1000000ull, s->barrier_timeouts.p,
+  // sticky: once a wait has timed out the counter is short of the missing arrivals for good, every later frame would
+  // spin for the full timeout and GPU 0's image may lack some ranks' tiles - refuse until the caller starts over
+  // (new shared block + rtp_peer_barrier_reset on every rank)
+  if (*(volatile int *)s->barrier_timeouts != 0)
+    return fail(RTP_ERR_STATE, "rtp_peer_barrier: an earlier frame barrier timed out (a rank did not arrive); the image of that "
+                               "frame is incomplete. Re-create the shared block and call rtp_peer_barrier_reset on every rank");
+  launch_peer_barrier((unsigned *)d_counter, target, (unsigned long long)timeout_ms * 1000000ull, s->barrier_timeouts_dev,
                       (cudaStream_t)stream);
   CK(cudaGetLastError());
   return RTP_OK;
@@ -733,11 +972,19 @@ int rtp_peer_barrier(rtp_scene *s, void *d_counter, uint32_t target, int timeout
 
 int rtp_peer_barrier_timeouts(rtp_scene *s) {
   if (!s) return fail(RTP_ERR_INVALID, "rtp_peer_barrier_timeouts: null scene");
-  if (!s->barrier_timeouts.p) return 0;
+  if (!s->barrier_timeouts) return 0;
   DeviceGuard g(s->device);
-  int n = 0;
-  CK(cudaMemcpy(&n, s->barrier_timeouts.p, sizeof n, cudaMemcpyDeviceToHost));  // waits for the device
-  return n;
+  CK(cudaDeviceSynchronize());  // barriers still in flight have finished (or given up) when this returns
+  return *(volatile int *)s->barrier_timeouts;
+}
+
+int rtp_peer_barrier_reset(rtp_scene *s) {
+  if (!s) return fail(RTP_ERR_INVALID, "rtp_peer_barrier_reset: null scene");
+  if (!s->barrier_timeouts) return RTP_OK;
+  DeviceGuard g(s->device);
+  CK(cudaDeviceSynchronize());
+  *s->barrier_timeouts = 0;
+  return RTP_OK;
 }
 
 int rtp_shared_open(int device, const void *handle, void **d_ptr) {
@@ -775,97 +1022,175 @@ int rtp_untile_device(rtp_scene *s, int width, int height, int world, const void
   return RTP_OK;
 }
 
+}  // extern "C"
+
+namespace {
+
+struct Planes {  // finished row-major image planes in device memory (of this or of another device); any may be null
+  float *rgb;
+  unsigned char *rgb8;
+  int *hit;
+};
+
+// Enqueues the share (rank of world) of the frame that scene s renders, resolved straight into dst.
+template <class AfterGroup>
+int enqueue_share(rtp_scene *s, const rtp_render_opts &o, int rank, int world, const Planes &dst, cudaStream_t cs,
+                  int *launches, AfterGroup after_group) {
+  const int n_px = own_tile_count(o.width, o.height, rank, world) * kTilePixels;
+  int rc = ensure_frame(s, s->frame, o.width, o.height, rank, world, std::max(o.max_depth, 1), n_px, true);
+  if (rc) return rc;
+  FrameParams p;
+  fill_params(s, s->frame, o, nullptr, p);
+  p.img_rgb = dst.rgb;
+  p.img_rgb8 = dst.rgb8;
+  p.img_hit = dst.hit;
+  return enqueue_frame(s, p, cs, launches, (o.flags & RTP_RENDER_PROFILE) != 0, s->frame.n_valid, world, after_group);
+}
+
+int ensure_staging(rtp_scene *s, size_t bytes) {
+  if (bytes <= s->staging_bytes) return RTP_OK;
+  if (s->staging) CK(cudaFreeHost(s->staging));
+  s->staging = nullptr;
+  s->staging_bytes = 0;
+  CK(cudaHostAlloc((void **)&s->staging, bytes, cudaHostAllocDefault));
+  s->staging_bytes = bytes;
+  return RTP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
 int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8, int32_t *hit, rtp_stats *st) {
   int rc = check_render_args(s, o);
   if (rc) return rc;
+  const bool multi = !s->peers.empty();
+  if (multi && o->world != 1)
+    return fail(RTP_ERR_INVALID, "rtp_render: a multi-device scene shards the frame itself (world must be 1)");
+  if (!rgb && !rgb8 && !hit && !st) return fail(RTP_ERR_INVALID, "rtp_render: no output requested");
   DeviceGuard g(s->device);
   cudaStream_t cs = s->stream;
   Frame &f = s->frame;
-  const int n_px = own_tile_count(o->width, o->height, o->rank, o->world) * kTilePixels;
-  rc = ensure_frame(s, f, o->width, o->height, o->rank, o->world, std::max(o->max_depth, 1), n_px, true);
-  if (rc) return rc;
-  CK(f.fb.ensure((size_t)std::max(n_px, 1)));
   const size_t npix = (size_t)o->width * o->height;
+  // the resolve kernel writes the finished row-major planes itself; they live on this (the first) device
   if (rgb) CK(f.out_rgb.ensure(npix * 3));
-  if (rgb8) CK(f.out_rgb8.ensure(npix * 3));
+  if (rgb8 || (!rgb && !hit)) CK(f.out_rgb8.ensure(npix * 3));  // statistics only: render into a scratch plane
   if (hit) CK(f.out_hit.ensure(npix));
-  // no float plane wanted: the resolve kernel writes the finished rgb8 / hit planes itself (no un-tile pass)
-  const bool fused = !rgb && (rgb8 || hit);
-  FrameParams p;
-  fill_params(s, f, *o, fused ? nullptr : f.fb.p, p);
-  if (o->world > 1) {  // other ranks' pixels stay untouched in the caller's buffers
-    if (rgb) CK(cudaMemcpyAsync(f.out_rgb.p, rgb, npix * 3 * sizeof(float), cudaMemcpyHostToDevice, cs));
-    if (rgb8) CK(cudaMemcpyAsync(f.out_rgb8.p, rgb8, npix * 3, cudaMemcpyHostToDevice, cs));
-    if (hit) CK(cudaMemcpyAsync(f.out_hit.p, hit, npix * sizeof(int), cudaMemcpyHostToDevice, cs));
-  }
-  if (fused) {
-    p.img_rgb8 = rgb8 ? f.out_rgb8.p : nullptr;
-    p.img_hit = hit ? f.out_hit.p : nullptr;
-  }
+  const Planes dst{rgb ? f.out_rgb.p : nullptr, (rgb8 || (!rgb && !hit)) ? f.out_rgb8.p : nullptr, hit ? f.out_hit.p : nullptr};
+  const int world = multi ? 1 + (int)s->peers.size() : o->world;
+  const int rank = multi ? 0 : o->rank;
   int launches = 0;
   CK(cudaEventRecord(s->ev[0], cs));
-  // one GPU, finished planes written by the resolve kernel: a tile group is a band of image rows, and its
-  // device-to-host copy starts on the group's stream as soon as that band is resolved, under the other
-  // groups' kernels
-  const bool banded = fused && o->world == 1;
-  const int tiles_x = f.tiles_x, width = o->width, height = o->height;
-  unsigned char *d_rgb8 = f.out_rgb8.p;
-  int *d_hit = f.out_hit.p;
+  // one GPU, whole frame: a tile group is a band of image rows, and its device-to-host copy starts on the group's
+  // stream as soon as that band is resolved, under the other groups' kernels
+  const bool banded = !multi && world == 1;
+  const int tiles_x = (o->width + kTileDim - 1) / kTileDim, width = o->width, height = o->height;
   auto copy_band = [=](int, int t0, int t1, cudaStream_t gs) -> cudaError_t {
     if (!banded || t1 <= t0) return cudaSuccess;
     const size_t y0 = (size_t)(t0 / tiles_x) * kTileDim;
     const size_t y1 = std::min<size_t>((size_t)height, (size_t)((t1 + tiles_x - 1) / tiles_x) * kTileDim);
     if (y1 <= y0) return cudaSuccess;
     cudaError_t e = cudaSuccess;
-    if (rgb8) e = cudaMemcpyAsync(rgb8 + y0 * width * 3, d_rgb8 + y0 * width * 3, (y1 - y0) * width * 3, cudaMemcpyDeviceToHost, gs);
+    if (rgb) e = cudaMemcpyAsync(rgb + y0 * width * 3, dst.rgb + y0 * width * 3, (y1 - y0) * width * 3 * sizeof(float), cudaMemcpyDeviceToHost, gs);
+    if (e == cudaSuccess && rgb8) e = cudaMemcpyAsync(rgb8 + y0 * width * 3, dst.rgb8 + y0 * width * 3, (y1 - y0) * width * 3, cudaMemcpyDeviceToHost, gs);
     if (e == cudaSuccess && hit)
-      e = cudaMemcpyAsync(hit + y0 * width, d_hit + y0 * width, (y1 - y0) * width * sizeof(int), cudaMemcpyDeviceToHost, gs);
+      e = cudaMemcpyAsync(hit + y0 * width, dst.hit + y0 * width, (y1 - y0) * width * sizeof(int), cudaMemcpyDeviceToHost, gs);
     return e;
   };
-  rc = enqueue_frame(s, p, cs, &launches, (o->flags & RTP_RENDER_PROFILE) != 0, f.n_valid, o->world, copy_band);
+  if (multi) {
+    // every other device renders its tiles on its own stream, fed by its own host thread, and stores them into this
+    // device's planes over NVLink (peer access); fork and join are CUDA events - no kernel waits for another
+    // (replaces the std::thread fan-out and join of raytraceScene, flyscene.cpp:266-289)
+    CK(cudaEventRecord(s->frame_start, cs));
+    for (size_t r = 0; r < s->peers.size(); ++r) {
+      rtp_scene *p = s->peers[r];
+      const rtp_render_opts opts = *o;
+      const int prank = (int)r + 1;
+      cudaEvent_t start = s->frame_start;
+      s->workers[r]->submit([p, opts, prank, world, dst, start]() -> int {
+        DeviceGuard pg(p->device);
+        int prc = RTP_OK;
+        cudaError_t e = cudaStreamWaitEvent(p->stream, start, 0);
+        if (e != cudaSuccess) prc = fail(RTP_ERR_CUDA, std::string("cudaStreamWaitEvent: ") + cudaGetErrorString(e));
+        int n = 0;
+        if (!prc) prc = enqueue_share(p, opts, prank, world, dst, p->stream, &n, [](int, int, int, cudaStream_t) { return cudaSuccess; });
+        if (!prc && (e = cudaEventRecord(p->frame_done, p->stream)) != cudaSuccess)
+          prc = fail(RTP_ERR_CUDA, std::string("cudaEventRecord: ") + cudaGetErrorString(e));
+        if (prc) p->err = g_err;
+        return prc;
+      });
+    }
+  }
+  rc = enqueue_share(s, *o, rank, world, dst, cs, &launches, copy_band);
+  if (multi) {
+    int wrc = RTP_OK;
+    for (size_t r = 0; r < s->peers.size(); ++r) {
+      const int prc = s->workers[r]->wait();
+      if (prc && !wrc) { wrc = prc; g_err = s->peers[r]->err; }
+    }
+    if (!rc) rc = wrc;
+    if (!rc)
+      for (rtp_scene *p : s->peers) CK(cudaStreamWaitEvent(cs, p->frame_done, 0));
+  }
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
-  if (banded) {
-    CK(cudaEventRecord(s->ev[2], cs));
-    // the frame's counters ride behind the frame on the same stream: one host wait for image and statistics
-    const bool quick_stats = st && !(o->flags & RTP_RENDER_PROFILE);
-    if (quick_stats) {
-      if (!s->counters_pinned) CK(cudaHostAlloc((void **)&s->counters_pinned, sizeof(int) * kCtrInts * kMaxGroups, cudaHostAllocDefault));
-      CK(cudaMemcpyAsync(s->counters_pinned, s->counters.p, sizeof(int) * kCtrInts * (size_t)s->last_groups, cudaMemcpyDeviceToHost, cs));
-    }
+  const bool quick_stats = st && !(o->flags & RTP_RENDER_PROFILE);
+  if (quick_stats) {  // the frame's counters ride behind the frame on the same stream: one host wait for image and statistics
+    if (!s->counters_pinned) CK(cudaHostAlloc((void **)&s->counters_pinned, sizeof(int) * kCtrInts * kMaxGroups, cudaHostAllocDefault));
+    CK(cudaMemcpyAsync(s->counters_pinned, s->counters.p, sizeof(int) * kCtrInts * (size_t)s->last_groups, cudaMemcpyDeviceToHost, cs));
+  }
+  const bool scatter = !multi && world > 1;  // one virtual rank of a sharded frame (tests, external multi-process drivers)
+  if (multi) {
+    if (rgb) CK(cudaMemcpyAsync(rgb, dst.rgb, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost, cs));
+    if (rgb8) CK(cudaMemcpyAsync(rgb8, dst.rgb8, npix * 3, cudaMemcpyDeviceToHost, cs));
+    if (hit) CK(cudaMemcpyAsync(hit, dst.hit, npix * sizeof(int), cudaMemcpyDeviceToHost, cs));
+  } else if (scatter) {
+    // only this rank's tiles were written on the device: the planes go to a page-locked staging block and the owned
+    // tiles are copied from there into the caller's buffers, whose other pixels stay untouched
+    const size_t o_rgb = 0, o_rgb8 = o_rgb + (rgb ? npix * 12 : 0), o_hit = (o_rgb8 + (rgb8 ? npix * 3 : 0) + 15) / 16 * 16;
+    rc = ensure_staging(s, o_hit + (hit ? npix * 4 : 0) + 16);
+    if (rc) return rc;
+    unsigned char *stg = (unsigned char *)s->staging;
+    if (rgb) CK(cudaMemcpyAsync(stg + o_rgb, dst.rgb, npix * 12, cudaMemcpyDeviceToHost, cs));
+    if (rgb8) CK(cudaMemcpyAsync(stg + o_rgb8, dst.rgb8, npix * 3, cudaMemcpyDeviceToHost, cs));
+    if (hit) CK(cudaMemcpyAsync(stg + o_hit, dst.hit, npix * 4, cudaMemcpyDeviceToHost, cs));
     CK(cudaStreamSynchronize(cs));
-    if (st) {
-      std::memset(st, 0, sizeof *st);
-      if (quick_stats) {
-        stats_from_counters(s, s->counters_pinned, std::max(s->last_groups, 1), s->last_primary, s->last_depth, s->last_lights, st);
-      } else {
-        rc = read_stats(s, st, cs);
-        if (rc) return rc;
+    for (int32_t t : f.tiles_host) {
+      const int x0 = (t % tiles_x) * kTileDim, y0 = (t / tiles_x) * kTileDim;
+      const int w = std::min(kTileDim, width - x0), y1 = std::min(height, y0 + kTileDim);
+      for (int y = y0; y < y1; ++y) {
+        const size_t at = (size_t)y * width + x0;
+        if (rgb) std::memcpy(rgb + 3 * at, stg + o_rgb + 12 * at, (size_t)w * 12);
+        if (rgb8) std::memcpy(rgb8 + 3 * at, stg + o_rgb8 + 3 * at, (size_t)w * 3);
+        if (hit) std::memcpy(hit + at, stg + o_hit + 4 * at, (size_t)w * 4);
       }
-      CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // includes the overlapped band copies
-      st->ms_total = st->ms_trace;
-      st->kernel_launches = launches;
     }
-    return RTP_OK;
   }
-  if (!fused && (rgb || rgb8 || hit)) {
-    launch_untile(f.fb.p, 0, f.local_of_tile.p, o->width, o->height, o->world, o->world > 1 ? o->rank : 0,
-                  rgb ? f.out_rgb.p : nullptr, rgb8 ? f.out_rgb8.p : nullptr, hit ? f.out_hit.p : nullptr, cs);
-    ++launches;
-    CK(cudaGetLastError());
-  }
-  CK(cudaEventRecord(s->ev[2], cs));
-  if (rgb) CK(cudaMemcpyAsync(rgb, f.out_rgb.p, npix * 3 * sizeof(float), cudaMemcpyDeviceToHost, cs));
-  if (rgb8) CK(cudaMemcpyAsync(rgb8, f.out_rgb8.p, npix * 3, cudaMemcpyDeviceToHost, cs));
-  if (hit) CK(cudaMemcpyAsync(hit, f.out_hit.p, npix * sizeof(int), cudaMemcpyDeviceToHost, cs));
   CK(cudaStreamSynchronize(cs));
   if (st) {
     std::memset(st, 0, sizeof *st);
-    rc = read_stats(s, st, cs);
-    if (rc) return rc;
-    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));
-    CK(cudaEventElapsedTime(&st->ms_total, s->ev[0], s->ev[2]));
+    if (quick_stats) {
+      stats_from_counters(s, s->counters_pinned, std::max(s->last_groups, 1), s->last_primary, s->last_depth, s->last_lights, st);
+    } else {
+      rc = read_stats(s, st, cs);
+      if (rc) return rc;
+    }
     st->kernel_launches = launches;
+    for (rtp_scene *p : s->peers) {  // the other devices' rays and launches
+      rtp_stats ps;
+      std::memset(&ps, 0, sizeof ps);
+      DeviceGuard pg(p->device);
+      rc = read_stats(p, &ps, p->stream);
+      if (rc) return rc;
+      st->rays_primary += ps.rays_primary; st->rays_shadow += ps.rays_shadow; st->rays_reflection += ps.rays_reflection;
+      st->hits += ps.hits;
+      st->ms_closest = std::max(st->ms_closest, ps.ms_closest);
+      st->ms_anyhit = std::max(st->ms_anyhit, ps.ms_anyhit);
+      st->ms_shade = std::max(st->ms_shade, ps.ms_shade);
+      st->kernel_launches += p->last_launches;
+    }
+    CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // one GPU: includes the overlapped band copies
+    st->ms_total = st->ms_trace;
   }
   return RTP_OK;
 }
@@ -968,6 +1293,11 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
   if (!s || !d_rays || n < 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device: bad argument");
   DeviceGuard g(s->device);
   cudaStream_t cs = (cudaStream_t)stream;
+  // one job at a time per scene (as enqueue_frame): the batch shares the scene's counter block and parked-ray list
+  // with the frames - closest-hit batches do park their stragglers on scenes larger than the L2
+  if (s->has_last && s->last_stream != cs) CK(cudaStreamSynchronize(s->last_stream));
+  s->last_stream = cs;
+  s->has_last = true;
   int *cursor = s->counters.p + kCtrAux;
   CK(cudaMemsetAsync(cursor, 0, sizeof(int), cs));
   CK(cudaMemsetAsync(s->counters.p + kCtrPark + 2 * 16, 0, 2 * sizeof(int), cs));
@@ -1002,6 +1332,16 @@ int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max
   if (!s || !rays || n <= 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays: bad argument");
   DeviceGuard g(s->device);
   cudaStream_t cs = s->stream;
+  {  // far origins need wider boxes (ensure_pad); |o| is known here, on the host
+    float dist = 0.f;
+    for (int64_t i = 0; i < n; ++i)
+      for (int c = 0; c < 3; ++c) {
+        const float a = std::fabs(rays[6 * i + c]);
+        if (a > dist && std::isfinite(a)) dist = a;
+      }
+    int prc = ensure_pad(s, dist);
+    if (prc) return prc;
+  }
   CK(s->rays_dev.ensure((size_t)n * 6));
   CK(cudaMemcpyAsync(s->rays_dev.p, rays, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, cs));
   if (mode == RTP_RAYS_CLOSEST) {
@@ -1048,8 +1388,10 @@ int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max
   rc = enqueue_frame(s, p, cs, &launches, false, (int)n, 1);
   if (rc) return rc;
   CK(cudaEventRecord(s->ev[1], cs));
-  std::vector<float4> h((size_t)n);
-  CK(cudaMemcpyAsync(h.data(), f.fb.p, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, cs));
+  rc = ensure_staging(s, (size_t)n * sizeof(float4));  // page-locked landing place of the (r, g, b, face) records
+  if (rc) return rc;
+  const float4 *h = (const float4 *)s->staging;
+  CK(cudaMemcpyAsync(s->staging, f.fb.p, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, cs));
   CK(cudaStreamSynchronize(cs));
   for (int64_t i = 0; i < n; ++i) {
     rgb[3 * i] = h[(size_t)i].x; rgb[3 * i + 1] = h[(size_t)i].y; rgb[3 * i + 2] = h[(size_t)i].z;

@@ -1,13 +1,18 @@
 // rtp_kernels.cu - hand-written sm_100a kernels for the ray-tracing hot path.
 //
 // Wavefront pipeline.  Per bounce level d:
-//   k_trace<FrameClosest>  calculateMinimumFace for every ray of the level (flyscene.cpp:373-396)
-//   k_prep                 per hit: P = o + t*d, interpolated normal, compaction (flyscene.cpp:464,572-600)
+//   k_trace<FrameClosest>  calculateMinimumFace for every ray of the level (flyscene.cpp:373-396).  At level 0 the
+//                          ray is generated from the pixel id when a lane takes it (traceRayThread + screenToWorld,
+//                          flyscene.cpp:299-314: a primary ray is a pure function of the pixel); when a ray retires, the
+//                          lane that still holds the triangle computes P = o + t*d and the interpolated normal
+//                          (flyscene.cpp:464,572-600) and appends the hit record to the compacted hit list.
 //   k_trace<FrameAny>      shadow() for every (hit, light) pair (flyscene.cpp:510-526)
 //   k_accum                calcSingleColor / calculateColor and the reflection-ray spawn
 //                          (flyscene.cpp:542-566,603-614,355-363)
-// plus k_raygen before level 0 (traceRayThread, flyscene.cpp:299-314) and k_resolve after the
-// last level (fold-back with the reference's ks-of-deepest-hit rule, flyscene.cpp:366-370).
+// and k_resolve_image after the last level (fold-back with the reference's ks-of-deepest-hit rule,
+// flyscene.cpp:366-370, quantise, store into the image).  With max_depth 1 the last two are ONE kernel
+// (k_shade_image): a frame is closest -> shadow -> shade+image, three dependent launches (+ k_coop).
+// (Round 1 ran k_raygen / k_prep / k_accum / k_resolve as four separate streaming kernels: 20 % of the C3 frame.)
 //
 // The two trace kernels are persistent: one CTA slot per SM resident set, every warp pulls rays
 // from a global cursor and REFILLS idle lanes (ballot + warp-aggregated atomic) whenever fewer
@@ -25,21 +30,51 @@ namespace {
 constexpr unsigned kFull = 0xffffffffu;
 
 // ---- jobs: where a trace kernel gets its rays from and where results go ----------------------
+// CAM = true: level 0 of a camera frame - ray q is pixel q of this rank's tile-major pixel list, generated here.
+// CAM = false: rays come from the level's ray list (reflection levels, caller-supplied rays).
+template <bool CAM>
 struct FrameClosest {
   static constexpr bool kAny = false;
+  static constexpr bool kSub = false;
   DeviceScene S;
+  // CAM
+  DeviceCamera cam;
+  const int *tile_ids;
+  int tiles_x, width, height;
+  // !CAM
   const float4 *ro, *rd;
-  float *hit_t;
+  // results: per ray the index of its hit record (-1 miss, -2 no ray); per hit record (P, triangle slot),
+  // (direction, pixel) and the path index.  CAM: record h of pixel q is q itself (the level's any-hit and shading
+  // kernels walk the pixels in order and skip the misses: neighbouring records are neighbouring pixels, no atomic
+  // in the retire path); otherwise the records are compacted (reflection levels lose most of their paths).
   int *hit_slot;
-  int *primface;  // depth 0 only
+  float4 *pbuf, *dbuf;
+  int *hitq;
+  int *hits_ctr;
+  int *primface;   // level 0 only: primary face id per pixel (-1 background, -2 pixel outside the image)
+  float4 *ksdeep;  // level 0 only: zeroed for pixels without a hit (k_accum / k_shade_image write the others)
   int *cursor;
   const int *count_ptr;  // device counter (depth > 0) or null
   int count_fixed;
   __device__ __forceinline__ int count() const { return count_ptr ? *count_ptr : count_fixed; }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    if (CAM) {
+      const int tile = __ldg(tile_ids + (q >> 10));
+      int x, y;
+      tile_pixel(q & (kTilePixels - 1), x, y);
+      const int i = (tile % tiles_x) * kTileDim + x;
+      const int j = (tile / tiles_x) * kTileDim + y;
+      if (i >= width || j >= height) {  // tile padding: pixel outside the image
+        hit_slot[q] = -2;
+        primface[q] = -2;
+        ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        return false;
+      }
+      trav_init(t, mk3(cam.eye[0], cam.eye[1], cam.eye[2]), primary_dir(cam, i, j), stack);
+      return true;
+    }
     const float4 d = rd[q];
-    if (d.w == 0.f) {  // no ray (pixel outside the image)
-      hit_t[q] = INFINITY;
+    if (d.w == 0.f) {  // no ray (padding of a caller-supplied batch; k_raygen set primface / ksdeep)
       hit_slot[q] = -2;
       return false;
     }
@@ -47,17 +82,57 @@ struct FrameClosest {
     return true;
   }
   __device__ __forceinline__ v3 box_origin(int, const Trav &t) const { return t.o; }
-  __device__ __forceinline__ bool finish(int q, Trav &t, int *stack) const;
+  // the deferred BoundingBox check of the winner (closest_needs_rerun): true = the ray runs again, careful
+  __device__ __forceinline__ bool rerun(Trav &t, int *stack) const { return closest_needs_rerun(S, t, stack); }
+  // Retires the rays of the lanes with fin set; called by all 32 lanes together.
+  __device__ __forceinline__ void commit(int q, const Trav &t, bool fin) const {
+    const int lane = threadIdx.x & 31;
+    const bool hit = fin && t.sbest >= 0;
+    const unsigned m = __ballot_sync(kFull, hit);
+    int h = q;
+    if (m) {
+      const int leader = __ffs(m) - 1;
+      if (CAM) {
+        if (lane == leader) atomicAdd(hits_ctr, __popc(m));  // statistics only: nobody waits for the result
+      } else {
+        if (lane == leader) h = atomicAdd(hits_ctr, __popc(m));
+        h = __shfl_sync(kFull, h, leader) + __popc(m & ((1u << lane) - 1u));
+      }
+    }
+    if (hit) {
+      const v3 P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
+      pbuf[h] = make_float4(P.x, P.y, P.z, i2f(t.sbest));
+      dbuf[h] = make_float4(t.d.x, t.d.y, t.d.z, i2f(CAM ? q : f2i(ro[q].w)));
+      if (!CAM) hitq[h] = q;
+    }
+    if (fin) {
+      hit_slot[q] = hit ? h : -1;
+      if (primface) {
+        primface[q] = hit ? __ldg(S.face_of + t.sbest) : -1;
+        if (!hit) ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
 };
 
+// DENSE: the level's hit records are indexed by pixel (camera rays): shadow ray q = pixel * n_lights + light, and pixels
+// without a hit have no shadow rays.  In batch mode the warp then takes 32 PIXELS from the cursor and walks the lights
+// itself (k_trace, kSubs): one atomic per 32 pixels whatever the light count, 32 rays towards the SAME light per batch
+// (coherent), and a batch of pixels without any hit costs a ballot, not n_lights trips to the cursor.
+template <bool DENSE>
 struct FrameAny {
   static constexpr bool kAny = true;
+  static constexpr bool kSub = DENSE;
   DeviceScene S;
   const float4 *pbuf;
   unsigned char *occl;
   int *cursor;
   const int *hits_ptr;
-  __device__ __forceinline__ int count() const { return *hits_ptr * S.n_lights; }
+  const int *hit_slot;  // DENSE: hit_slot[pixel] < 0 = no hit, no shadow ray
+  int n_px;             // DENSE: pixels of the level
+  __device__ __forceinline__ int units() const { return n_px; }
+  __device__ __forceinline__ int subs() const { return S.n_lights; }
+  __device__ __forceinline__ int count() const { return (DENSE ? n_px : *hits_ptr) * S.n_lights; }
   __device__ __forceinline__ v3 light_dir(int q, v3 P) const {
     const int li = q % S.n_lights;
     const float4 l0 = __ldg(S.lights + 2 * li);
@@ -66,17 +141,21 @@ struct FrameAny {
     return L;
   }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
-    const v3 P = xyz(pbuf[q / S.n_lights]);
+    const int h = q / S.n_lights;
+    if (DENSE && hit_slot[h] < 0) return false;
+    const v3 P = xyz(pbuf[h]);
     const v3 L = light_dir(q, P);
     trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);  // flyscene.cpp:512
     return true;
   }
   __device__ __forceinline__ v3 box_origin(int q, const Trav &) const { return xyz(pbuf[q / S.n_lights]); }
-  __device__ __forceinline__ bool finish(int q, Trav &t, int *) const { occl[q] = t.sbest >= 0 ? 1 : 0; return true; }
+  __device__ __forceinline__ bool rerun(Trav &, int *) const { return false; }
+  __device__ __forceinline__ void commit(int q, const Trav &t, bool fin) const { if (fin) occl[q] = t.sbest >= 0 ? 1 : 0; }
 };
 
 struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
   static constexpr bool kAny = false;
+  static constexpr bool kSub = false;
   DeviceScene S;
   const float *rays;
   int *face;
@@ -90,11 +169,17 @@ struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
     return true;
   }
   __device__ __forceinline__ v3 box_origin(int, const Trav &t) const { return t.o; }
-  __device__ __forceinline__ bool finish(int q, Trav &t, int *stack) const;
+  __device__ __forceinline__ bool rerun(Trav &t, int *stack) const { return closest_needs_rerun(S, t, stack); }
+  __device__ __forceinline__ void commit(int q, const Trav &t, bool fin) const {
+    if (!fin) return;
+    face[q] = t.sbest >= 0 ? __ldg(S.face_of + t.sbest) : -1;
+    if (tout) tout[q] = t.tbest;
+  }
 };
 
 struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
   static constexpr bool kAny = true;
+  static constexpr bool kSub = false;
   DeviceScene S;
   const float *rays;
   unsigned char *occ;
@@ -111,22 +196,9 @@ struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
     const float *r = rays + 6 * (size_t)q;
     return mk3(r[0], r[1], r[2]);
   }
-  __device__ __forceinline__ bool finish(int q, Trav &t, int *) const { occ[q] = t.sbest >= 0 ? 1 : 0; return true; }
+  __device__ __forceinline__ bool rerun(Trav &, int *) const { return false; }
+  __device__ __forceinline__ void commit(int q, const Trav &t, bool fin) const { if (fin) occ[q] = t.sbest >= 0 ? 1 : 0; }
 };
-
-__device__ __forceinline__ bool FrameClosest::finish(int q, Trav &t, int *stack) const {
-  if (closest_needs_rerun(S, t, stack)) return false;  // keeps running in careful mode
-  hit_t[q] = t.tbest;
-  hit_slot[q] = t.sbest;
-  if (primface) primface[q] = t.sbest >= 0 ? __ldg(S.face_of + t.sbest) : -1;
-  return true;
-}
-__device__ __forceinline__ bool RaysClosest::finish(int q, Trav &t, int *stack) const {
-  if (closest_needs_rerun(S, t, stack)) return false;
-  face[q] = t.sbest >= 0 ? __ldg(S.face_of + t.sbest) : -1;
-  if (tout) tout[q] = t.tbest;
-  return true;
-}
 
 // ---- stragglers: step budget, parking list, warp-cooperative traversal (k_coop) ------------------
 // A ray that is still running when every other lane of its warp has finished is a chain of
@@ -264,7 +336,13 @@ template <class Job, int kRefillBelow>
 __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, const ParkList pl) {
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
-  const int count = job.count();
+  // kSubs (batch mode of a job with sub-batches): the cursor hands out 32 UNITS (pixels) and the warp walks each
+  // unit's `n_sub` rays (lights) itself: ray q = unit * n_sub + sub
+  constexpr bool kSubs = Job::kSub && kRefillBelow == 1;
+  int n_sub = 1, sub = 1, ubase = 0;
+  if constexpr (kSubs) { n_sub = job.subs(); sub = n_sub; }
+  int count;
+  if constexpr (kSubs) count = job.units(); else count = job.count();
 #ifdef RTP_TRACE_TIMING
   const unsigned long long tm_start = gtime();
   unsigned long long tm_fetch = tm_start;
@@ -280,8 +358,30 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
     if (__popc(act) < kRefillBelow) {
       // retire: every lane whose traversal has ended writes its result NOW, together - the deferred
       // BoundingBox check of a closest hit is ~60 instructions and used to run one lane at a time
-      if (have && t.node == kSentinel) have = !job.finish(q, t, stack);  // false: careful re-run, node = root again
+      bool fin = have && t.node == kSentinel;
+      if (fin && job.rerun(t, stack)) fin = false;  // careful re-run: node = root again
+      job.commit(q, t, fin);                        // all lanes: the warp's hit records are appended together
+      if (fin) have = false;
       act = __ballot_sync(kFull, have);
+      if constexpr (kSubs) {
+        if (act == 0 && (!exhausted || sub < n_sub)) {
+          if (sub >= n_sub) {  // next 32 units
+            int base = 0;
+            if (lane == 0) base = atomicAdd(job.cursor, 32);
+            ubase = __shfl_sync(kFull, base, 0);
+            exhausted = ubase + 32 >= count;
+            sub = 0;
+          }
+          const int u = ubase + lane;
+          if (u < count) {
+            q = u * n_sub + sub;
+            have = job.init(q, t, stack);
+          }
+          act = __ballot_sync(kFull, have);
+          sub = (sub == 0 && act == 0) ? n_sub : sub + 1;  // no unit of the batch has rays at all: skip its other subs
+          age = 0;
+        }
+      } else
       if (!exhausted && __popc(act) < kRefillBelow) {
         // refill every idle lane with the next rays of the global list
         const unsigned need = ~act;
@@ -303,7 +403,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
       }
     }
     if (act == 0) {
-      if (exhausted) break;
+      if (exhausted && sub >= n_sub) break;
       continue;
     }
     if (++age > pl.budget && __popc(act) <= pl.lanes) {
@@ -353,7 +453,7 @@ __global__ void __launch_bounds__(128, 4) k_coop(const Job job, const ParkList p
   int *const ws = s_ws[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   const int n_parked = min(*pl.ctr, pl.cap);
-  int stack[1];  // job.finish -> closest_needs_rerun -> trav_init writes stack[0] only
+  int stack[1];  // job.rerun -> closest_needs_rerun -> trav_init writes stack[0] only
   for (;;) {
     int k = 0;
     if (lane == 0) k = atomicAdd(pl.ctr + 1, 1);
@@ -370,105 +470,80 @@ __global__ void __launch_bounds__(128, 4) k_coop(const Job job, const ParkList p
     __syncwarp();
     for (;;) {
       coop_trace<Job::kAny>(job.S, t, job.box_origin(q, t), ws, n);
-      if (job.finish(q, t, stack)) break;
+      if (!job.rerun(t, stack)) break;
       if (lane == 0) ws[0] = 0;  // closest-hit: the winner's box failed - start over from the root, careful
       n = 1;
       __syncwarp();
     }
+    job.commit(q, t, lane == 0);  // every lane holds the same ray: one of them retires it
     __syncwarp();
   }
 }
 
 // ---- streaming kernels ----------------------------------------------------------------------------
-// Depth-0 rays: pixel (i, j) of an owned screen tile through the camera (traceRayThread,
-// flyscene.cpp:301-308), or the q-th caller-supplied ray (traceRay API).
+// Depth-0 rays of a caller-supplied batch (traceRay API): the q-th ray into the level-0 ray list.  Camera frames do not
+// come through here: their primary rays are generated inside k_trace (FrameClosest<true>::init).
 __global__ void __launch_bounds__(256) k_raygen(const FrameParams p) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= p.n_px) return;
-  v3 o, d = mk3(0.f, 0.f, 0.f);
-  bool valid;
-  if (p.user_rays) {
-    valid = q < p.n_user_rays;
-    const float *r = p.user_rays + 6 * (size_t)(valid ? q : 0);
-    o = mk3(r[0], r[1], r[2]);
-    d = mk3(r[3], r[4], r[5]);
-  } else {
-    const int tile = __ldg(p.tile_ids + (q >> 10));
-    int x, y;
-    tile_pixel(q & (kTilePixels - 1), x, y);
-    const int i = (tile % p.tiles_x) * kTileDim + x;
-    const int j = (tile / p.tiles_x) * kTileDim + y;
-    o = mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
-    valid = i < p.width && j < p.height;
-    if (valid) d = primary_dir(p.cam, i, j);
-  }
-  p.ray_o[0][q] = make_float4(o.x, o.y, o.z, i2f(q));
-  p.ray_d[0][q] = make_float4(d.x, d.y, d.z, valid ? 1.f : 0.f);
+  const bool valid = q < p.n_user_rays;
+  const float *r = p.user_rays + 6 * (size_t)(valid ? q : 0);
+  p.ray_o[0][q] = make_float4(r[0], r[1], r[2], i2f(q));
+  p.ray_d[0][q] = make_float4(r[3], r[4], r[5], valid ? 1.f : 0.f);
   p.ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
   p.primface[q] = valid ? -1 : -2;
 }
 
-// Per ray of the level that hit something: P, interpolated normal, and a slot in the compacted
-// hit list (warp-aggregated append keeps neighbouring pixels together).
-__global__ void __launch_bounds__(256) k_prep(const FrameParams p, const int depth) {
-  const int lane = threadIdx.x & 31;
-  const int count = depth == 0 ? p.n_px : p.counters[kCtrPaths + depth];
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (blockIdx.x * blockDim.x >= count) return;  // block-uniform
-  const int slot = q < count ? p.hit_slot[q] : -1;
-  const bool hit = slot >= 0;
-  v3 P = mk3(0.f, 0.f, 0.f), N = P;
-  if (hit) {
-    const v3 o = xyz(p.ray_o[depth & 1][q]), d = xyz(p.ray_d[depth & 1][q]);
-    P = vadd(o, vmuls(d, p.hit_t[q]));  // flyscene.cpp:464
-    N = interpolate_normal_slot(p.S, slot, P);
+// calculateColor for hit record h (flyscene.cpp:603-614): interpolated normal (flyscene.cpp:572-600), Phong over the
+// unshadowed lights, clamped.  ks_out: the material's specular colour (the reflection weight of SURVEY.md Q5).
+__device__ __forceinline__ v3 shade_hit(const FrameParams &p, int h, v3 o, v3 P, int slot, v3 &normal, float4 &ks_out) {
+  normal = interpolate_normal_slot(p.S, slot, P);
+  const unsigned mat = (unsigned)f2i(__ldg(p.S.tris + 4 * (size_t)slot + 2).w) & kTriMatMask;
+  const float4 m0 = __ldg(p.S.materials + 3 * mat), m1 = __ldg(p.S.materials + 3 * mat + 1),
+               m2 = __ldg(p.S.materials + 3 * mat + 2);
+  const int n_lights = p.S.n_lights;
+  v3 sum = mk3(0.f, 0.f, 0.f);
+  for (int li = 0; li < n_lights; ++li) {  // calculateColor, flyscene.cpp:606-612
+    if (p.occl[(size_t)h * n_lights + li]) continue;  // shadowed: contributes nothing (:543-545)
+    const float4 l0 = __ldg(p.S.lights + 2 * li), l1 = __ldg(p.S.lights + 2 * li + 1);
+    v3 L = xyz(l0);
+    if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // :607
+    sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, normal, L, xyz(l1), o, P));
   }
-  const unsigned m = __ballot_sync(kFull, hit);
-  if (m) {
-    const int leader = __ffs(m) - 1;
-    int h = 0;
-    if (lane == leader) h = atomicAdd(p.counters + kCtrHits + depth, __popc(m));
-    h = __shfl_sync(kFull, h, leader) + __popc(m & ((1u << lane) - 1u));
-    if (hit) {
-      p.hitlist[h] = q;
-      p.pbuf[h] = make_float4(P.x, P.y, P.z, i2f(slot));
-      p.nbuf[h] = make_float4(N.x, N.y, N.z, 0.f);
-    }
-  }
+  ks_out = m2;
+  return mk3(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z));
 }
 
-// Per hit: Phong over the unshadowed lights, clamp, remember ks, spawn the reflection ray.
+// origin of path q at `depth` (camera frames: the eye at depth 0; otherwise the level's ray list)
+__device__ __forceinline__ v3 path_origin(const FrameParams &p, int depth, int q) {
+  if (depth == 0 && !p.user_rays) return mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+  return xyz(p.ray_o[depth & 1][q]);
+}
+
+// the hit records of camera rays (level 0 of a frame) are dense over the pixels, all others are compacted
+__device__ __forceinline__ bool dense_level(const FrameParams &p, int depth) { return depth == 0 && !p.user_rays; }
+
+// Per hit: normal, Phong over the unshadowed lights, clamp, remember ks, spawn the reflection ray.
 __global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int depth) {
   const int lane = threadIdx.x & 31;
-  const int count = p.counters[kCtrHits + depth];
+  const bool dense = dense_level(p, depth);
+  const int count = dense ? p.n_px : p.counters[kCtrHits + depth];
   const int h = blockIdx.x * blockDim.x + threadIdx.x;
   if (blockIdx.x * blockDim.x >= count) return;  // block-uniform
-  const bool live = h < count;
+  const bool live = h < count && (!dense || p.hit_slot[h] >= 0);
   const bool spawn = live && depth + 1 < p.max_depth;
   v3 o2 = mk3(0.f, 0.f, 0.f), r = o2;
   int pixel = 0;
   if (live) {
-    const int q = p.hitlist[h];
-    const float4 ro = p.ray_o[depth & 1][q];
-    const v3 o = xyz(ro), d = xyz(p.ray_d[depth & 1][q]);
-    pixel = f2i(ro.w);
-    const float4 pb = p.pbuf[h];
-    const v3 P = xyz(pb), normal = xyz(p.nbuf[h]);
-    const int slot = f2i(pb.w);
-    const unsigned mat = (unsigned)f2i(__ldg(p.S.tris + 4 * (size_t)slot + 2).w) & kTriMatMask;
-    const float4 m0 = __ldg(p.S.materials + 3 * mat), m1 = __ldg(p.S.materials + 3 * mat + 1),
-                 m2 = __ldg(p.S.materials + 3 * mat + 2);
-    const int n_lights = p.S.n_lights;
-    v3 sum = mk3(0.f, 0.f, 0.f);
-    for (int li = 0; li < n_lights; ++li) {  // calculateColor, flyscene.cpp:606-612
-      if (p.occl[(size_t)h * n_lights + li]) continue;  // shadowed: contributes nothing (:543-545)
-      const float4 l0 = __ldg(p.S.lights + 2 * li), l1 = __ldg(p.S.lights + 2 * li + 1);
-      v3 L = xyz(l0);
-      if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // :607
-      sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, normal, L, xyz(l1), o, P));
-    }
-    p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
-    p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
+    const float4 pb = p.pbuf[h], db = p.dbuf[h];
+    const v3 P = xyz(pb), d = xyz(db);
+    pixel = f2i(db.w);
+    const v3 o = path_origin(p, depth, dense ? h : p.hitq[h]);
+    float4 ks;
+    v3 normal;
+    const v3 c = shade_hit(p, h, o, P, f2i(pb.w), normal, ks);
+    p.direct[(size_t)depth * p.n_px + pixel] = make_float4(c.x, c.y, c.z, 0.f);
+    p.ksdeep[pixel] = make_float4(ks.x, ks.y, ks.z, i2f(depth + 1));
     if (spawn) {
       r = reflect_dir(d, normal);            // :361
       o2 = vadd(P, vmuls(r, (float)0.001));  // :362
@@ -513,10 +588,26 @@ __device__ __forceinline__ unsigned char quantise(float c) {
   return (unsigned char)min(255, max(qv, 0));
 }
 
+// max_depth 1: there is one level, so the shading of its hits (k_accum) and the fold (clamp(direct + 0 * ks), the
+// deepest-level case of resolve_pixel) are done here, per pixel, without the round trip through direct[] / ksdeep[].
+__device__ __forceinline__ float4 shade_pixel_depth1(const FrameParams &p, int q) {
+  const int face = p.primface[q];
+  if (face == -2) return make_float4(0.f, 0.f, 0.f, i2f(-2));  // pixel outside the image / no ray
+  const int h = p.hit_slot[q];
+  if (h < 0) return make_float4(p.bg[0], p.bg[1], p.bg[2], i2f(-1));  // flyscene.cpp:327-330
+  const float4 pb = p.pbuf[h];
+  float4 ks;
+  v3 normal;
+  const v3 dc = shade_hit(p, h, path_origin(p, 0, q), xyz(pb), f2i(pb.w), normal, ks);
+  return make_float4(clamp01(fadd(dc.x, fmul(0.f, ks.x))), clamp01(fadd(dc.y, fmul(0.f, ks.y))),
+                     clamp01(fadd(dc.z, fmul(0.f, ks.z))), i2f(face));
+}
+
+template <bool SHADE1>
 __global__ void __launch_bounds__(256) k_resolve(const FrameParams p) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= p.n_px) return;
-  float4 out = resolve_pixel(p, q);
+  float4 out = SHADE1 ? shade_pixel_depth1(p, q) : resolve_pixel(p, q);
   if (f2i(out.w) == -2) out.w = i2f(-1);
   p.fb[q] = out;
 }
@@ -524,6 +615,8 @@ __global__ void __launch_bounds__(256) k_resolve(const FrameParams p) {
 // Resolve fused with the image assembly: thread r of a tile handles pixel (r & 31, r >> 5) of that
 // tile, so a warp writes 32 consecutive pixels of one image row (96 contiguous bytes) - the image may
 // be peer memory on GPU 0, reached over NVLink, and then this kernel IS the framebuffer gather.
+// SHADE1 (max_depth 1): k_shade_image - the level's shading is done here too (shade_pixel_depth1).
+template <bool SHADE1>
 __global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= p.n_px) return;  // n_px is a multiple of 1024: whole warps leave together
@@ -534,9 +627,14 @@ __global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
   const bool valid = i < p.width && j < p.height;
   const int q = (local << 10) + ((((y >> 2) * 4 + (x >> 3)) << 5) + ((y & 3) << 3) + (x & 7));
   float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (valid) out = resolve_pixel(p, q);
+  if (valid) out = SHADE1 ? shade_pixel_depth1(p, q) : resolve_pixel(p, q);
   const size_t idx = (size_t)j * p.width + i;
   if (valid && p.fb) p.fb[q] = out;
+  if (valid && p.img_rgb) {  // float plane, row-major: a warp stores 384 consecutive bytes
+    p.img_rgb[3 * idx] = out.x;
+    p.img_rgb[3 * idx + 1] = out.y;
+    p.img_rgb[3 * idx + 2] = out.z;
+  }
   if (p.img_rgb8) {
     // the warp's 32 pixels are 96 consecutive bytes of one image row: lanes 0-23 store them as 24 aligned words
     // (one full-width transaction towards HBM, a peer GPU over NVLink or page-locked host memory over PCIe)
@@ -607,6 +705,21 @@ __global__ void k_peer_barrier(unsigned *counter, unsigned target, unsigned long
   __threadfence_system();
 }
 
+// Grows the padding of every child box of the hierarchy by `extra` (in place, once, when a camera or a ray batch
+// starts so far from the scene that the rounding of P = o + t*d exceeds the padding the tree was built with:
+// ulp(|o|) grows with the distance, the build-time pad does not).  Unbounded boxes (non-finite faces) stay as they are.
+__global__ void __launch_bounds__(256) k_inflate_nodes(float4 *nodes, int n_nodes, float extra) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_nodes) return;
+  auto lo = [&](float v) { return fabsf(v) < 3.0e38f ? v - extra : v; };
+  auto hi = [&](float v) { return fabsf(v) < 3.0e38f ? v + extra : v; };
+  float4 *N = nodes + 4 * (size_t)i;
+  float4 a = N[0], b = N[1], c = N[2];
+  N[0] = make_float4(lo(a.x), hi(a.y), lo(a.z), hi(a.w));
+  N[1] = make_float4(lo(b.x), hi(b.y), lo(b.z), hi(b.w));
+  N[2] = make_float4(lo(c.x), hi(c.y), lo(c.z), hi(c.w));
+}
+
 int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning runs)
 // Straggler policy (measured on B200, profiles/r01_tail.md): parking pays for closest-hit launches on
 // scenes that do not fit the L2 (cold nodes make the serial chain slow: C3 closest-hit 0.47 -> 0.40 ms);
@@ -661,11 +774,8 @@ int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters
   pl.budget = park ? (Job::kAny ? g_budget_any : g_budget) : 0x3fffffff;
   pl.lanes = Job::kAny ? g_park_lanes_any : g_park_lanes;
   if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job, pl);
-  else if (refill <= 4) k_trace<Job, 4><<<blocks, threads, 0, st>>>(job, pl);
   else if (refill <= 8) k_trace<Job, 8><<<blocks, threads, 0, st>>>(job, pl);
-  else if (refill <= 16) k_trace<Job, 16><<<blocks, threads, 0, st>>>(job, pl);
-  else if (refill <= 24) k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
-  else k_trace<Job, 32><<<blocks, threads, 0, st>>>(job, pl);
+  else k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
   if (pl.budget >= 0x3fffffff) return 1;
   k_coop<Job><<<cfg.blocks_coop, 128, 0, st>>>(job, pl);
   return 2;
@@ -681,8 +791,8 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
     if (t == 32 || t == 64 || t == 128) cfg.threads = t;
   }
   int b0 = 1, b1 = 1;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_trace<FrameClosest, 24>, cfg.threads, 0);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny, 24>, cfg.threads, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b0, k_trace<FrameClosest<true>, 1>, cfg.threads, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny<true>, 1>, cfg.threads, 0);
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
   cfg.blocks_coop = sms * 2;
@@ -693,34 +803,53 @@ void launch_peer_barrier(unsigned *counter, unsigned target, unsigned long long 
   k_peer_barrier<<<1, 1, 0, st>>>(counter, target, timeout_ns, timeouts);
 }
 
+void launch_inflate_nodes(float4 *nodes, int n_nodes, float extra, cudaStream_t st) {
+  if (n_nodes > 0) k_inflate_nodes<<<(n_nodes + 255) / 256, 256, 0, st>>>(nodes, n_nodes, extra);
+}
+
 void launch_raygen(const FrameParams &p, cudaStream_t st) { k_raygen<<<(p.n_px + 255) / 256, 256, 0, st>>>(p); }
 
-int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
-  FrameClosest j;
+template <bool CAM>
+static int launch_closest_t(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+  FrameClosest<CAM> j;
   j.S = p.S;
+  j.cam = p.cam;
+  j.tile_ids = p.tile_ids;
+  j.tiles_x = p.tiles_x; j.width = p.width; j.height = p.height;
   j.ro = p.ray_o[depth & 1];
   j.rd = p.ray_d[depth & 1];
-  j.hit_t = p.hit_t;
   j.hit_slot = p.hit_slot;
+  j.pbuf = p.pbuf; j.dbuf = p.dbuf; j.hitq = p.hitq;
+  j.hits_ctr = p.counters + kCtrHits + depth;
   j.primface = depth == 0 ? p.primface : nullptr;
+  j.ksdeep = p.ksdeep;
   j.cursor = p.counters + kCtrFetchClosest + depth;
   j.count_ptr = depth == 0 ? nullptr : p.counters + kCtrPaths + depth;
   j.count_fixed = p.n_px;
   return launch_trace(j, cfg.blocks_closest, cfg, p.counters, depth, depth == 0 && !p.user_rays, p.n_px, st);
 }
 
-void launch_prep(const FrameParams &p, int depth, cudaStream_t st) {
-  k_prep<<<(p.n_px + 255) / 256, 256, 0, st>>>(p, depth);
+int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+  if (depth == 0 && !p.user_rays) return launch_closest_t<true>(p, depth, cfg, st);
+  return launch_closest_t<false>(p, depth, cfg, st);
 }
 
-int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
-  FrameAny j;
+template <bool DENSE>
+static int launch_anyhit_t(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+  FrameAny<DENSE> j;
   j.S = p.S;
   j.pbuf = p.pbuf;
   j.occl = p.occl;
   j.cursor = p.counters + kCtrFetchAny + depth;
   j.hits_ptr = p.counters + kCtrHits + depth;
+  j.hit_slot = p.hit_slot;
+  j.n_px = p.n_px;
   return launch_trace(j, cfg.blocks_any, cfg, p.counters, 8 + depth, depth == 0 && !p.user_rays, p.n_px, st);
+}
+
+int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
+  if (depth == 0 && !p.user_rays) return launch_anyhit_t<true>(p, depth, cfg, st);  // camera level: dense records
+  return launch_anyhit_t<false>(p, depth, cfg, st);
 }
 
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
@@ -728,8 +857,15 @@ void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {
 }
 
 void launch_resolve(const FrameParams &p, cudaStream_t st) {
-  if (p.img_rgb8 || p.img_hit) k_resolve_image<<<(p.n_px + 255) / 256, 256, 0, st>>>(p);
-  else k_resolve<<<(p.n_px + 255) / 256, 256, 0, st>>>(p);
+  const int blocks = (p.n_px + 255) / 256;
+  const bool image = p.img_rgb || p.img_rgb8 || p.img_hit;
+  if (p.max_depth == 1) {  // the level's shading happens in the same kernel (no k_accum)
+    if (image) k_resolve_image<true><<<blocks, 256, 0, st>>>(p);
+    else k_resolve<true><<<blocks, 256, 0, st>>>(p);
+  } else {
+    if (image) k_resolve_image<false><<<blocks, 256, 0, st>>>(p);
+    else k_resolve<false><<<blocks, 256, 0, st>>>(p);
+  }
 }
 
 void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile, int width, int height,

@@ -28,6 +28,7 @@ struct FrameParams {
   int max_depth;
   float bg[3];
   float4 *fb;        // out, tile-major: r, g, b, bit-cast primary face id (may be null when img_* is set)
+  float *img_rgb;           // out, optional: the finished image as floats, row-major W x H x 3
   unsigned char *img_rgb8;  // out, optional: the finished image, row-major W x H x 3, quantised like the PPM writer;
   int *img_hit;             //   and the primary face ids, W x H.  Either may live on ANOTHER GPU (peer memory
                             //   mapped through CUDA IPC): every rank stores its own tiles straight into GPU 0's image
@@ -36,11 +37,10 @@ struct FrameParams {
   float4 *direct;    // [max_depth][n_px] clamped direct colour per depth
   float4 *ray_o[2];  // ping-pong ray lists: (origin, bit-cast local pixel)
   float4 *ray_d[2];  //                      (direction, 1 = live / 0 = no ray)
-  float *hit_t;      // [n_px] closest-hit t of the current depth
-  int *hit_slot;     // [n_px] closest-hit triangle slot (-1 miss, -2 no ray)
-  int *hitlist;      // [n_px] compacted list of paths that hit something at the current depth
-  float4 *pbuf;      // [n_px] per hit: (P, bit-cast triangle slot)
-  float4 *nbuf;      // [n_px] per hit: (interpolated normal, -)
+  int *hit_slot;     // [n_px] per path of the current depth: index of its hit record (-1 miss, -2 no ray)
+  float4 *pbuf;      // [n_px] per hit record: (P, bit-cast triangle slot)
+  float4 *dbuf;      //        (ray direction, bit-cast local pixel)
+  int *hitq;         //        path index at this depth (compacted levels; a camera level's record h is pixel h)
   unsigned char *occl;  // [n_px * n_lights] per hit and light: 1 = shadowed
   int *counters;
 };
@@ -53,23 +53,26 @@ struct LaunchCfg {
 };
 void query_launch_cfg(int device, LaunchCfg &cfg);
 
-// depth-0 rays of every owned pixel (traceRayThread, flyscene.cpp:299-314) or the caller's rays
+// depth-0 rays of a caller-supplied batch into the ray list (camera frames generate theirs inside launch_closest)
 void launch_raygen(const FrameParams &p, cudaStream_t st);
-// calculateMinimumFace for every ray of `depth` (flyscene.cpp:373-396); returns the kernels launched
-// (k_trace, plus k_coop when stragglers are parked)
+// calculateMinimumFace for every ray of `depth` (flyscene.cpp:373-396), at depth 0 of a camera frame with the ray
+// generation of traceRayThread (flyscene.cpp:299-314); per hit P, interpolated normal and the compacted hit record
+// (flyscene.cpp:464,572-600).  Returns the kernels launched (k_trace, plus k_coop when stragglers are parked)
 int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
-// per hit: P, interpolated normal, compaction (flyscene.cpp:464,572-600)
-void launch_prep(const FrameParams &p, int depth, cudaStream_t st);
 // shadow() for every (hit, light) pair (flyscene.cpp:510-526)
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
-// calcSingleColor / calculateColor + reflection-ray spawn (flyscene.cpp:542-566,603-614,355-363)
+// calcSingleColor / calculateColor + reflection-ray spawn (flyscene.cpp:542-566,603-614,355-363); not needed when
+// max_depth is 1 (launch_resolve shades the single level itself)
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st);
-// fold-back of the per-depth colours (flyscene.cpp:366-370) -> tile-major framebuffer
+// fold-back of the per-depth colours (flyscene.cpp:366-370) -> tile-major framebuffer and / or the finished image planes
 void launch_resolve(const FrameParams &p, cudaStream_t st);
 // tile-major buffers of all ranks -> row-major planes (any of the outputs may be null).
 // only_rank >= 0: `all` holds just that rank's tiles; pixels of other ranks are left untouched.
 void launch_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile, int width, int height,
                    int world, int only_rank, float *rgb, unsigned char *rgb8, int *hit, cudaStream_t st);
+
+// widens every child box of the hierarchy by `extra` (far cameras / ray origins: see k_inflate_nodes)
+void launch_inflate_nodes(float4 *nodes, int n_nodes, float extra, cudaStream_t st);
 
 // arrive-and-wait of one rank on a counter in (peer) device memory; see k_peer_barrier
 void launch_peer_barrier(unsigned *counter, unsigned target, unsigned long long timeout_ns, int *timeouts, cudaStream_t st);

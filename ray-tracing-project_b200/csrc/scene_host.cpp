@@ -173,6 +173,7 @@ std::string flatten_scene(const rtp_mesh &m, HostScene &out, int n_threads, bool
   float pad_rel = 3e-5f;
   if (const char *e = std::getenv("RTP_BVH_PAD")) pad_rel = (float)std::atof(e);
   out.pad = pad_rel * maxabs;
+  out.maxabs = maxabs;
   if (!with_bvh) {  // rank order; the device builder sorts, fits and permutes (bvh_build_gpu.cu)
     out.n_nodes = 0;
     out.bvh_depth = 0;

@@ -39,6 +39,7 @@ struct HostScene {
   int n_flagged = 0;     // triangles that need the zero-normal check
   int n_degenerate = 0;  // triangles whose face normal is not finite/unit (edge-case list)
   float pad = 0.f;       // AABB padding used
+  float maxabs = 1.f;    // largest finite |coordinate| of the world-space vertices (the pad is relative to it)
   float scene_lo[3] = {0, 0, 0}, scene_hi[3] = {0, 0, 0};  // bounds of the finite (unpadded) triangles
 };
 

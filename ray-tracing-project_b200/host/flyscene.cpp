@@ -103,7 +103,15 @@ bool Flyscene::uploadScene() {
   m.min_faces = MIN_FACES; m.max_boxes = MAX_BOXES;
   if (scene) rtp_scene_destroy(scene);
   scene = nullptr;
-  if (rtp_scene_create(&m, DEVICE, &scene) != RTP_OK) return fail("rtp_scene_create");
+  if (DEVICES <= 1) {
+    if (rtp_scene_create(&m, DEVICE, &scene) != RTP_OK) return fail("rtp_scene_create");
+    return true;
+  }
+  const int ndev = rtp_device_count();
+  if (ndev <= 0) return fail("rtp_device_count");
+  std::vector<int> devs((size_t)DEVICES);
+  for (int r = 0; r < DEVICES; ++r) devs[(size_t)r] = ((DEVICE < 0 ? 0 : DEVICE) + r) % ndev;
+  if (rtp_scene_create_multi(&m, devs.data(), DEVICES, &scene) != RTP_OK) return fail("rtp_scene_create_multi");
   return true;
 }
 
@@ -136,7 +144,7 @@ void Flyscene::raytraceScene(int width, int height) {  // flyscene.cpp:250-297
   std::cout << "ray tracing ..." << std::endl;
   const std::clock_t wall0 = std::clock();
   const time_t start_time = time(NULL);
-  if (width == 0 && height == 0) {
+  if (width == 0 || height == 0) {  // flyscene.cpp:255
     raytracing_image_size = flycamera.getViewportSize();
   } else {
     raytracing_image_size = Eigen::Vector2i(width, height);
@@ -297,41 +305,4 @@ void Flyscene::createDebugRay(const Eigen::Vector2f &mouse_pos) {  // flyscene.c
   std::tuple<Tucano::Face, Eigen::Vector3f, float> hit = calculateMinimumFace(origin, dir, RENDER_DEBUG_BOXES);
   if (std::get<2>(hit) == INFINITY) return;
   debugChain.push_back(std::get<1>(hit));
-}
-
-void Flyscene::addLight() {  // flyscene.cpp:182-248
-  float r, g, b;
-  std::string l = "";
-  std::cout << " What colour do you want in rgb format? (Enter three numbers seperately between 1 and 0)" << std::endl;
-  std::cin >> r >> g >> b;
-  while (std::cin.fail()) {
-    if (std::cin.eof()) return;
-    std::cout << "Error" << std::endl;
-    std::cin.clear();
-    std::cin.ignore(256, '\n');
-    std::cin >> r >> g >> b;
-  }
-  while (!(l == "s" || l == "p" || l == "d")) {
-    std::cout << " Do you want a spherical, directional or a point light? (s, d or p)" << std::endl;
-    if (!(std::cin >> l)) return;
-  }
-  if (l == "s" || l == "p") {
-    std::pair<Eigen::Vector3f, Eigen::Vector3f> light(flycamera.getCenter(), Eigen::Vector3f(r, g, b));
-    if (l == "s") {
-      std::string radius, n;
-      std::cout << "What Radius?" << std::endl;
-      if (!(std::cin >> radius)) return;
-      std::cout << "How many point light for approximations?" << std::endl;
-      if (!(std::cin >> n)) return;
-      int Nlights = std::stoi(n);
-      sphericalLight(light, std::stof(radius), Nlights);
-      light.second /= (float)(Nlights + 1);
-    }
-    lights.push_back(light);
-  }
-  if (l == "d") {
-    Eigen::Vector3f direction = flycamera.screenToWorld(Eigen::Vector2f(flycamera.getViewport()(2) / 2, flycamera.getViewport()(3) / 2));
-    dirLights.push_back(std::make_tuple(direction, Eigen::Vector3f(r, g, b), Eigen::Quaternion<float>(flycamera.getRotationMatrix())));
-  }
-  std::cout << "Created a light with color spectrum (r,g,b): (" << r << ", " << g << ", " << b << ")" << std::endl;
 }

@@ -42,8 +42,10 @@ class Flyscene {
 
   Tucano::Flycamera *getCamera(void) { return &flycamera; }
 
-  // Interactive light prompt on stdin, as the reference (flyscene.cpp:182-248).
-  void addLight();
+  // The reference's interactive stdin light prompt (flyscene.cpp:182-248) belongs to its GLFW key loop
+  // (main.cpp:70-71), which is out of scope: declared for source compatibility, does nothing.
+  // Lights are set through the public `lights` / `dirLights` members and sphericalLight().
+  void addLight() {}
 
   // Traces the ray through the pixel under mouse_pos and keeps its hit chain in debugChain
   // (the reference draws it as cylinders; flyscene.cpp:129-173).
@@ -126,7 +128,11 @@ class Flyscene {
   std::string OUTPUT_NAME = "result.ppm";       // flyscene.cpp:292; empty: no file
   std::string OUTPUT_PNG_NAME = "";             // non-empty: also write an 8-bit RGB PNG of it
   std::string OUTPUT_BINARY_NAME = "";          // non-empty: also write a binary P6 PPM of the device-quantised image
-  int DEVICE = -1;                               // CUDA ordinal (-1: current device)
+  int DEVICE = -1;                               // CUDA ordinal of the first GPU (-1: current device)
+  // GPUs the frame is fanned out over - the role Flyscene::THREADS row bands play in the reference (flyscene.cpp:266-289):
+  // interleaved 32x32 screen tiles, rank r on device (DEVICE + r) % device count (more ranks than devices: ranks share
+  // a GPU), every rank storing its pixels into the first GPU's image.  Same image for every value.  Set before initialize().
+  int DEVICES = 1;
 
   static const bool RENDER_BOUNDINGBOXES = false;
   static const bool RENDER_BOUNDINGBOX_COLORED_TRIANGLES = false;

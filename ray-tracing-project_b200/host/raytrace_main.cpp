@@ -7,7 +7,9 @@
 //            [--soft x y z r g b RADIUS N] [--seed S]   soft light: N jittered point lights (libc rand, or with --seed
 //                                            the counter-based generator of Flyscene::sphericalLightSeeded)
 //            [--out result.ppm] [--out-p6 result_p6.ppm] [--out-png result.png] [--device N] [--dump-scene PREFIX] [--dump-lights PREFIX]
-//            [--serial-obj]                  with --dump-scene: the line-by-line OBJ loader instead of the parallel one
+//            [--gpus N]                      shard the frame over N devices (DEVICE, DEVICE + 1, ... modulo the device count:
+//                                            with N above the device count ranks share a GPU); same image as --gpus 1
+//            [--srand S]                     seed libc rand() before --soft lights are drawn (flyscene.cpp:529-538 uses rand())
 //            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
 //            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
 //            [--png-from-u8 IN.u8 OUT.png]   W*H*3 bytes -> PNG (no GPU)
@@ -20,80 +22,17 @@
 #include <string>
 
 #include "flyscene.hpp"
+#include "scene_dump.hpp"
 
 namespace {
 
-template <class T>
-void dump(const std::string &path, const std::vector<T> &v) {
-  FILE *f = fopen(path.c_str(), "wb");
-  if (!f) { perror(path.c_str()); exit(3); }
-  if (!v.empty()) fwrite(v.data(), sizeof(T), v.size(), f);
-  fclose(f);
-}
+using scene_dump::dump;
 
 int usage() {
   fprintf(stderr, "usage: raytrace [--model path.obj] [--size W H] [--depth D] [--fovy deg] [--view 12 floats]\n"
                   "                [--light x y z r g b] [--dirlight x y z r g b] [--nolights] [--soft x y z r g b radius n]\n"
-                  "                [--out file.ppm] [--device n] [--dump-scene prefix]\n");
+                  "                [--srand S] [--seed S] [--out file.ppm] [--device n] [--gpus N] [--dump-scene prefix]\n");
   return 2;
-}
-
-// Loads and flattens exactly as Flyscene::initialize does, without touching CUDA.
-int dump_scene(const std::string &model, const std::string &prefix, int min_faces, bool serial_obj, bool load_only) {
-  Tucano::Mesh mesh;
-  std::vector<Tucano::Material::Mtl> materials;
-  const auto t0 = std::chrono::steady_clock::now();
-  if (serial_obj) Tucano::MeshImporter::loadObjFileSerial(mesh, materials, model);
-  else Tucano::MeshImporter::loadObjFile(mesh, materials, model);
-  fprintf(stderr, "obj load (%s): %.3f s\n", serial_obj ? "serial" : "parallel",
-          std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count());
-  if (load_only) min_faces = INT_MAX;  // --dump-scene-noboxes: one box, no splitter (timing / large synthetic meshes)
-  mesh.normalizeModelMatrix();
-  const int V = mesh.getNumberOfVertices(), F = mesh.getNumberOfFaces();
-  if (F == 0) return 1;
-  std::vector<float> verts, normals, fnormal, mats, shape;
-  std::vector<int> faces, fmat;
-  for (int i = 0; i < V; ++i) {
-    for (int c = 0; c < 4; ++c) verts.push_back(mesh.getVertex(i)[c]);
-    for (int c = 0; c < 3; ++c) normals.push_back(mesh.getNormal(i)[c]);
-  }
-  for (int i = 0; i < F; ++i) {
-    const Tucano::Face &f = mesh.getFace(i);
-    for (int c = 0; c < 3; ++c) { faces.push_back((int)f.vertex_ids[(size_t)c]); fnormal.push_back(f.normal[c]); }
-    fmat.push_back(f.material_id);
-  }
-  for (const Tucano::Material::Mtl &m : materials) {
-    for (int c = 0; c < 3; ++c) mats.push_back(m.getAmbient()[c]);
-    for (int c = 0; c < 3; ++c) mats.push_back(m.getDiffuse()[c]);
-    for (int c = 0; c < 3; ++c) mats.push_back(m.getSpecular()[c]);
-    mats.push_back(m.getShininess()); mats.push_back(m.getOpticalDensity()); mats.push_back(m.getDissolveFactor());
-  }
-  const Eigen::Affine3f sm = mesh.getShapeModelMatrix();
-  shape.assign(sm.data(), sm.data() + 12);
-  // the BoundingBox list through the mirror class, as Flyscene::generateBoundingBoxes drives it
-  BoundingBox::mesh = &mesh;
-  BoundingBox *root = new BoundingBox(true);
-  root->fitMesh();
-  bool notDone = true;
-  while (notDone) {
-    notDone = false;
-    std::vector<BoundingBox *> current = BoundingBox::boxes;
-    for (BoundingBox *b : current)
-      if (b->getNumberOfFaces() > min_faces && (!b->failed[0] || !b->failed[1] || !b->failed[2])) {
-        BoundingBox *nb = b->splitBox();
-        while (b == nb) nb = b->splitBox();
-        notDone = true;
-      }
-  }
-  std::vector<float> bounds;
-  std::vector<int> box_off, box_faces;
-  BoundingBox::exportBoxes(bounds, box_off, box_faces);
-  BoundingBox::deconstruct();
-  dump(prefix + ".verts.f32", verts); dump(prefix + ".normals.f32", normals); dump(prefix + ".fnormal.f32", fnormal);
-  dump(prefix + ".materials.f32", mats); dump(prefix + ".shape.f32", shape); dump(prefix + ".faces.i32", faces);
-  dump(prefix + ".fmat.i32", fmat); dump(prefix + ".boxes.f32", bounds); dump(prefix + ".box_off.i32", box_off);
-  dump(prefix + ".box_faces.i32", box_faces);
-  return 0;
 }
 
 // Primary rays exactly as traceRayThread forms them (flyscene.cpp:301-308), host side only.
@@ -144,7 +83,8 @@ int main(int argc, char **argv) {
   bool seeded = false;
   int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
   float fovy = 60.f;
-  bool has_view = false, nolights = false, serial_obj = false, load_only = false;
+  bool has_view = false, nolights = false, load_only = false;
+  int gpus = 1;
   float view[12];
   std::vector<std::array<float, 6>> lights, dirlights;
   std::vector<std::array<float, 8>> soft;
@@ -164,7 +104,8 @@ int main(int argc, char **argv) {
     else if (a == "--dump-lights") { need(i, 1); lights_prefix = argv[++i]; }
     else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
     else if (a == "--dump-scene-noboxes") { need(i, 1); dump_prefix = argv[++i]; load_only = true; }
-    else if (a == "--serial-obj") serial_obj = true;
+    else if (a == "--gpus") { need(i, 1); gpus = atoi(argv[++i]); }
+    else if (a == "--srand") { need(i, 1); srand((unsigned)strtoul(argv[++i], nullptr, 10)); }
     else if (a == "--dump-rays") { need(i, 1); rays_prefix = argv[++i]; }
     else if (a == "--ppm-from-f32") { need(i, 2); f32_in = argv[++i]; f32_out = argv[++i]; }
     else if (a == "--nolights") nolights = true;
@@ -181,7 +122,10 @@ int main(int argc, char **argv) {
       soft.push_back(l);
     } else return usage();
   }
-  if (!dump_prefix.empty()) return dump_scene(model, dump_prefix, 300, serial_obj, load_only);
+  if (!dump_prefix.empty())
+    return scene_dump::dump_scene(model, dump_prefix, 300, load_only,
+                                  [](Tucano::Mesh &m, std::vector<Tucano::Material::Mtl> &mt, const std::string &f) { Tucano::MeshImporter::loadObjFile(m, mt, f); },
+                                  "parallel");
   if (!rays_prefix.empty()) return dump_rays(rays_prefix, W, H, fovy, has_view ? view : nullptr);
   if (!f32_in.empty()) return ppm_from_f32(f32_in, f32_out, W, H);
   if (!u8_in.empty()) {  // W*H*3 bytes -> PNG (no GPU): the writer's own test hook
@@ -198,6 +142,7 @@ int main(int argc, char **argv) {
   flyscene->OBJECT_NAME = slash == std::string::npos ? model : model.substr(slash + 1);
   flyscene->OUTPUT_NAME = out;
   flyscene->DEVICE = device;
+  flyscene->DEVICES = gpus;
   flyscene->max_depth = depth;
   flyscene->initialize(W, H);
   if (!flyscene->ok()) { fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str()); return 1; }

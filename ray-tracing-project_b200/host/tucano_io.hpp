@@ -1,8 +1,8 @@
 // tucano_io.hpp - input and output formats of the ray-tracing path (included by tucano_lite.hpp):
 //   MaterialImporter::loadMTL      utils/mtlIO.hpp:49-140
 //   MeshImporter::computeNormals   utils/objimporter.hpp:81-106
-//   MeshImporter::loadObjFile      utils/objimporter.hpp:117-351 (mapped file, parsed in parallel; loadObjFileSerial
-//                                  is the line-by-line original)
+//   MeshImporter::loadObjFile      utils/objimporter.hpp:117-351 (mapped file, parsed in parallel; the line-by-line
+//                                  cross-check loader lives with the tests: tests/hostsim/obj_serial_loader.hpp)
 //   ImageImporter::writePPMImage   utils/ppmIO.hpp:135-156
 // The parsing rules are the reference's, quirks included: `vn` lines are used per
 // VERTEX index and only when #vn == #v, otherwise smooth normals are rebuilt from unit face
@@ -97,86 +97,6 @@ inline void computeNormals(const std::vector<Eigen::Vector4f> &vertices, const s
     }
   }
   for (size_t i = 0; i < normals.size(); ++i) normals[i].normalize();
-}
-
-// The reference's loader, line by line through iostreams (objimporter.hpp:117-351).  Kept as the cross-check of
-// loadObjFile below (tests/test_host_mirror.py: both must fill the Mesh with the same bits).
-inline void loadObjFileSerial(Tucano::Mesh &mesh, std::vector<Tucano::Material::Mtl> &mtls, std::string filename) {
-  std::string path = MaterialImporter::getPathName(filename);
-  std::vector<Eigen::Vector4f> vert;
-  std::vector<Eigen::Vector3f> norm;
-  std::vector<int> elements_material_id;
-  std::vector<std::vector<GLuint>> elementsVertices;
-  std::ifstream in(filename.c_str(), std::ios::in);
-  if (!in) {
-    std::cerr << "Cannot open " << filename.c_str() << std::endl;
-    return;
-  }
-  elementsVertices.push_back(std::vector<GLuint>());
-  elements_material_id.push_back(-1);
-  std::string line;
-  int current_mat = -1;
-  while (getline(in, line)) {
-    if (line.substr(0, 6) == "mtllib" && line.size() > 7) {
-      std::string mtlfn = path + line.substr(7);
-      MaterialImporter::stripEol(mtlfn);
-      MaterialImporter::loadMTL(mtls, mtlfn);
-    } else if (line.substr(0, 6) == "usemtl" && line.size() > 7) {
-      if (!elementsVertices.back().empty()) {
-        elementsVertices.push_back(std::vector<GLuint>());
-        elements_material_id.push_back(-1);
-      }
-      std::string name = line.substr(7);
-      MaterialImporter::stripEol(name);
-      for (size_t i = 0; i < mtls.size(); ++i)
-        if (mtls[i].getName().compare(name) == 0) current_mat = (int)i;
-      elements_material_id.back() = current_mat;
-    } else if (line.substr(0, 2) == "v ") {
-      std::istringstream s(line.substr(2));
-      Eigen::Vector4f v;
-      s >> v[0]; s >> v[1]; s >> v[2]; v[3] = 1.0f;
-      vert.push_back(v);  // per-vertex colours after xyz are only used by the GL preview
-    } else if (line.substr(0, 2) == "vn" && line.size() > 3) {
-      std::istringstream s(line.substr(3));
-      Eigen::Vector3f vn;
-      s >> vn[0]; s >> vn[1]; s >> vn[2];
-      norm.push_back(vn);
-    } else if (line.substr(0, 2) == "f ") {
-      std::stringstream liness(line.substr(2));
-      std::string buf, element;
-      while (liness >> buf) {  // "v", "v/t", "v//n" or "v/t/n": only the vertex id feeds the ray tracer
-        std::stringstream elementss(buf);
-        std::getline(elementss, element, '/');
-        int vertexId = 0;
-        try { vertexId = std::stoi(element); } catch (...) { continue; }
-        elementsVertices.back().push_back((GLuint)(vertexId - 1));
-      }
-    }
-  }
-  in.close();
-  if (vert.size() > 0) {
-    mesh.loadVertices(vert);
-    mesh.storeVertexData(vert);
-  }
-  if (norm.size() != vert.size()) {
-    norm.clear();
-    computeNormals(vert, elementsVertices, norm);
-  }
-  if (norm.size() == vert.size()) {
-    mesh.loadNormals(norm);
-    mesh.storeNormalData(norm);
-  }
-  for (size_t i = 0; i < elementsVertices.size(); ++i) {
-    if (elementsVertices[i].size() > 0) {
-      mesh.loadIndices(elementsVertices[i], elements_material_id[i]);
-      mesh.storeVertexIdsData(elementsVertices[i]);
-    }
-  }
-  mesh.createFaces();
-  std::cout << "OBJ info:" << std::endl;
-  std::cout << "number vertices : " << mesh.getNumberOfVertices() << std::endl;
-  std::cout << "number faces : " << mesh.getNumberOfFaces() << std::endl;
-  std::cout << "number materials : " << mesh.getNumberOfMaterials() << std::endl;
 }
 
 // ---- OBJ ingest at scale -------------------------------------------------------
@@ -316,7 +236,7 @@ inline void loadObjFile(Tucano::Mesh &mesh, std::vector<Tucano::Material::Mtl> &
   const char *data = size ? (const char *)mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0) : nullptr;
   if (size && data == MAP_FAILED) {
     ::close(fd);
-    loadObjFileSerial(mesh, mtls, filename);
+    std::cerr << "Cannot map " << filename.c_str() << std::endl;
     return;
   }
   // one range per thread, cut at line starts

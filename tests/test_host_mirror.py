@@ -34,6 +34,23 @@ def need_cli():
         pytest.skip("raytrace CLI not built (python -c 'import __graft_entry__ as g; g.build()')")
 
 
+SERIAL_TOOL = os.path.join(ROOT, "tests", "hostsim", "obj_dump_serial")
+
+
+def serial_dump_tool():
+    """tests/hostsim/obj_dump_serial: the line-by-line cross-check loader (test infrastructure), built on demand."""
+    host = os.path.join(ROOT, "ray-tracing-project_b200", "host")
+    csrc = os.path.join(ROOT, "ray-tracing-project_b200", "csrc")
+    srcs = [os.path.join(ROOT, "tests", "hostsim", "obj_dump_serial.cpp"), os.path.join(host, "BoundingBox.cpp"),
+            os.path.join(csrc, "ref_boxes.cpp")]
+    deps = srcs + [os.path.join(ROOT, "tests", "hostsim", "obj_serial_loader.hpp")] + \
+        [os.path.join(host, f) for f in os.listdir(host) if f.endswith((".h", ".hpp"))]
+    if not os.path.exists(SERIAL_TOOL) or any(os.path.getmtime(d) > os.path.getmtime(SERIAL_TOOL) for d in deps):
+        subprocess.check_call(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-I", csrc, "-I", os.path.join(ROOT, "include"),
+                               "-I/usr/local/cuda/include", "-o", SERIAL_TOOL] + srcs + ["-lpthread"])
+    return SERIAL_TOOL
+
+
 def bits(a):
     a = np.ascontiguousarray(a)
     return a.view(np.uint32) if a.dtype == np.float32 else a
@@ -187,7 +204,7 @@ def test_parallel_obj_ingest_equals_the_line_by_line_loader(name, tmp_path):
         path = model_path(name)
     flag = "--dump-scene"
     ref = str(tmp_path / "serial")
-    r = subprocess.run([CLI, "--model", path, flag, ref, "--serial-obj"], capture_output=True, text=True)
+    r = subprocess.run([serial_dump_tool(), path, ref], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     for threads, chunk in ((1, 1 << 16), (3, 64), (8, 17), (8, 1 << 16)):
         pre = str(tmp_path / f"par{threads}_{chunk}")
@@ -319,7 +336,7 @@ def test_parallel_obj_ingest_fuzz(seed, tmp_path):
     open(path, "w", newline="").write(random_obj_text(seed))
     open(str(tmp_path / "quirks.mtl"), "w").write(open(os.path.join(GOLDEN, "quirks.mtl")).read())
     ref = str(tmp_path / "serial")
-    r = subprocess.run([CLI, "--model", path, "--dump-scene", ref, "--serial-obj"], capture_output=True, text=True)
+    r = subprocess.run([serial_dump_tool(), path, ref], capture_output=True, text=True)
     if r.returncode != 0:
         pytest.skip("no faces in this file")
     for threads, chunk in ((4, 32), (8, 7)):
