@@ -77,9 +77,10 @@ def build_workload(name, synth):
         m = synth.terrain(708)
         return dict(mesh=m, w=1920, h=1080, max_depth=1, lights=synth.LIGHT_DEFAULT, ao=64, eye=(0.0, 0.30, 0.20),
                     view=synth.look_at((0.0, 0.30, 0.20), (0.0, -0.05, -0.08)),
-                    desc="C5: incoherent stress on the C3 terrain (1002528 triangles): from every primary hit of the "
-                         "1920x1080 frame 64 directions uniform on the hemisphere around the face normal "
-                         "(Philox, seed 1234), any-hit queries (= Flyscene::shadow)")
+                    desc="C5: incoherent stress on the C3 terrain (1002528 triangles): from every primary hit point of the "
+                         "1920x1080 frame (moved 0.003 along the interpolated normal) 64 directions uniform on the "
+                         "hemisphere around that normal, Philox4x32-10 keyed by (seed 1234, pixel index): the same ray "
+                         "set for every GPU count; any-hit queries (= Flyscene::shadow)")
     raise SystemExit(f"unknown workload {name}")
 
 
@@ -471,27 +472,24 @@ def run_c5(args, wl, rtp):
     scene.set_camera(w, h, wl["view"])
     info = scene.info()
     stream = torch.cuda.current_stream().cuda_stream
-    # hit points + geometric normals of the primary frame (workload generation, untimed)
-    eye = np.asarray(wl["eye"], np.float32)
+    # workload generation (untimed): primary hit points and interpolated normals of the frame, then the rays of this
+    # rank's contiguous share of the hit pixels from the counter-based generator (synth.ao_rays_pixels: keyed by the
+    # pixel index, so the union over the ranks is the same ray set whatever the GPU count)
+    synth = importlib.import_module("ray-tracing-project_b200.synth")
     out = scene.render(w, h, max_depth=1, want=("hit",))
     hit = out["hit"].ravel()
     keep = np.nonzero(hit >= 0)[0]
     share = np.array_split(keep, world)[rank]
-    f = np.asarray(m["faces"])[hit[share]]
-    shp = np.asarray(m["shape"], np.float32).reshape(3, 4)
-    V = (np.asarray(m["verts"], np.float32)[:, :3] @ shp[:, :3].T + shp[:, 3]).astype(np.float32)
-    P = torch.from_numpy((V[f[:, 0]] + V[f[:, 1]] + V[f[:, 2]]) / np.float32(3)).to(dev)  # centroid of the hit triangle
-    n = np.cross(V[f[:, 1]] - V[f[:, 0]], V[f[:, 2]] - V[f[:, 0]])
-    n /= np.maximum(np.linalg.norm(n, axis=1, keepdims=True), 1e-30)
-    N = torch.from_numpy(n.astype(np.float32)).to(dev)
-    N = torch.where(((torch.from_numpy(eye).to(dev)[None, :] - P) * N).sum(1, keepdim=True) < 0, -N, N)
-    g = torch.Generator(device=dev)
-    g.manual_seed(1234 + rank)
-    d = torch.randn((len(share), n_ao, 3), device=dev, generator=g)
-    d = d / d.norm(dim=2, keepdim=True)
-    d = torch.where((d * N[:, None, :]).sum(2, keepdim=True) < 0, -d, d)
-    o = (P + 0.003 * N)[:, None, :].expand(-1, n_ao, -1)
-    rays = torch.cat([o, d], 2).reshape(-1, 6).contiguous()
+    eye, dirs = synth.camera_rays(w, h, wl["view"])
+    P_np = synth.primary_hit_points(m, hit[share], eye, dirs[share])
+    N_np = synth.shading_normals(m, hit[share], P_np)
+    del dirs
+    P_t, N_t, pix_t = torch.from_numpy(P_np).to(dev), torch.from_numpy(N_np).to(dev), torch.from_numpy(share.astype(np.int64)).to(dev)
+    rays = torch.empty((len(share) * n_ao, 6), dtype=torch.float32, device=dev)
+    for c0 in range(0, len(share), 1 << 17):  # chunks bound the generator's int64 temporaries
+        c1 = min(len(share), c0 + (1 << 17))
+        rays[c0 * n_ao:c1 * n_ao] = synth.ao_rays_pixels(P_t[c0:c1], N_t[c0:c1], pix_t[c0:c1], n_per_point=n_ao, xp=torch)
+    ray_crc = int(rays.view(torch.int32).to(torch.int64).sum().item()) & 0xffffffffffff  # order-free checksum of the share
     n_rays = rays.shape[0]
     occ = torch.zeros(n_rays, dtype=torch.uint8, device=dev)
     ao = torch.zeros(len(share), dtype=torch.float32, device=dev)
@@ -522,10 +520,11 @@ def run_c5(args, wl, rtp):
     for _ in range(max(args.warmup, 3)):
         step()
     sync_all()
-    total = torch.tensor([n_rays], dtype=torch.int64, device=dev)
+    total = torch.tensor([n_rays, ray_crc], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(total)
-    rays_step = int(total.item())
+    rays_step = int(total[0].item())
+    ray_crc = int(total[1].item()) & 0xffffffffffff
     t_begin = time.perf_counter()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ms_steps = []
@@ -572,6 +571,7 @@ def run_c5(args, wl, rtp):
                     ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
                     dtype="f32", data="synthetic",
                     config=dict(workload=wl["desc"], rays_per_step=rays_step, triangles=n_tris, bvh_nodes=info["n_bvh_nodes"],
+                                ray_set_checksum=f"{ray_crc:012x} (sum of the rays' float bits over all ranks, mod 2^48: equal for every GPU count)",
                                 parallelism=f"rays{world}" if world > 1 else "1gpu",
                                 l2="256 MiB memset between timed steps (untimed); the 3.2 GB ray list alone exceeds the L2"),
                     clocks=clocks,

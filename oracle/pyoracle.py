@@ -226,7 +226,7 @@ def ref_model(name):
 
 def ref_run(obj, w, h, view=None, fovy=60.0, point_lights=None, dir_lights=None, max_depth=2,
             pixels=None, stride=None, procs=1, dump_scene=False, chain=True, mode="render", rays=None,
-            keep_dir=None, repeat=1):
+            keep_dir=None, repeat=1, soft=None, srand=None):
     """Run the reference binary. Returns dict of numpy arrays (+ 'mesh' when dump_scene)."""
     if not ref_available():
         raise RuntimeError("oracle/_ref/ref_harness not built (run `make -C oracle ref` where /root/reference exists)")
@@ -243,6 +243,10 @@ def ref_run(obj, w, h, view=None, fovy=60.0, point_lights=None, dir_lights=None,
             lines.append("light " + " ".join(repr(float(x)) for x in l))
         for l in _f32(dir_lights if dir_lights is not None else np.zeros((0, 6)), (-1, 6)):
             lines.append("dirlight " + " ".join(repr(float(x)) for x in l))
+    if srand is not None:
+        lines.append(f"srand {int(srand)}")
+    for l in (soft if soft is not None else []):  # x y z r g b radius n: the reference's sphericalLight + addLight "s" branch
+        lines.append("soft " + " ".join(repr(float(x)) for x in np.asarray(l, np.float32)))
     if pixels is not None:
         _i32(pixels, (-1, 2)).tofile(pre + ".pxin.i32")
         lines.append(f"pixel_file {pre}.pxin.i32")
@@ -276,6 +280,7 @@ def ref_run(obj, w, h, view=None, fovy=60.0, point_lights=None, dir_lights=None,
         tt = open(pre + ".time.txt").read().split()
         out["trace_seconds"] = float(tt[0])
     out["hit"], out["t"] = ld(".hit.i32", np.int32), ld(".t.f32", np.float32)
+    out["lights"] = ld(".lights.f32", np.float32, (-1, 6))  # Flyscene::lights as traced (after sphericalLight)
     if dump_scene:
         m = Mesh(ld(".verts.f32", np.float32), ld(".normals.f32", np.float32), ld(".faces.i32", np.int32),
                  ld(".face_mat.i32", np.int32), ld(".materials.f32", np.float32), ld(".face_normal.f32", np.float32),

@@ -40,6 +40,11 @@ struct Job {
   int max_depth = 2;
   bool lights_given = false;
   std::vector<std::array<float, 6>> lights, dirlights;
+  // soft lights: x y z r g b radius n -> the reference's own Flyscene::sphericalLight (flyscene.cpp:529-538, libc
+  // rand()) followed by what the "s" branch of its addLight does with the light itself (flyscene.cpp:213-236)
+  std::vector<std::array<float, 8>> soft;
+  bool has_srand = false;
+  unsigned srand_seed = 1;
   // pixel selection
   int stride_x = 1, stride_y = 1, off_x = 0, off_y = 0;
   std::string pixel_file;   // int32 (i,j) pairs, overrides strides
@@ -68,6 +73,8 @@ bool parse_job(const char* path, Job& j) {
     else if (k == "nolights") j.lights_given = true;
     else if (k == "light") { std::array<float, 6> l; for (auto& v : l) s >> v; j.lights.push_back(l); j.lights_given = true; }
     else if (k == "dirlight") { std::array<float, 6> l; for (auto& v : l) s >> v; j.dirlights.push_back(l); j.lights_given = true; }
+    else if (k == "soft") { std::array<float, 8> l; for (auto& v : l) s >> v; j.soft.push_back(l); j.lights_given = true; }
+    else if (k == "srand") { s >> j.srand_seed; j.has_srand = true; }
     else if (k == "stride") s >> j.stride_x >> j.stride_y >> j.off_x >> j.off_y;
     else if (k == "pixel_file") s >> j.pixel_file;
     else if (k == "ray_file") s >> j.ray_file;
@@ -177,6 +184,19 @@ int main(int argc, char** argv) {
       fs.dirLights.push_back(std::make_tuple(Eigen::Vector3f(l[0], l[1], l[2]),
                                              Eigen::Vector3f(l[3], l[4], l[5]),
                                              Eigen::Quaternionf::Identity()));
+  }
+  if (job.has_srand) srand(job.srand_seed);
+  for (auto& l : job.soft) {
+    std::pair<Eigen::Vector3f, Eigen::Vector3f> light(Eigen::Vector3f(l[0], l[1], l[2]), Eigen::Vector3f(l[3], l[4], l[5]));
+    const int n = (int)l[7];
+    fs.sphericalLight(light, l[6], n);  // the reference's own code
+    light.second /= (n + 1);            // flyscene.cpp:234
+    fs.lights.push_back(light);         // flyscene.cpp:237
+  }
+  {  // the light list the frame is traced with (Flyscene::lights, in order)
+    std::vector<float> lf;
+    for (auto& l : fs.lights) { for (int c = 0; c < 3; ++c) lf.push_back(l.first(c)); for (int c = 0; c < 3; ++c) lf.push_back(l.second(c)); }
+    write_bin(job.out + ".lights.f32", lf.data(), lf.size());
   }
   std::string rmcmd = "rm -rf " + sdir;
 

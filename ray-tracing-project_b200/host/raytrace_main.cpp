@@ -9,6 +9,7 @@
 //            [--out result.ppm] [--out-p6 result_p6.ppm] [--out-png result.png] [--device N] [--dump-scene PREFIX] [--dump-lights PREFIX]
 //            [--gpus N]                      shard the frame over N devices (DEVICE, DEVICE + 1, ... modulo the device count:
 //                                            with N above the device count ranks share a GPU); same image as --gpus 1
+//            [--lights-only]                 with --dump-lights: build the light list and stop (no scene, no GPU)
 //            [--srand S]                     seed libc rand() before --soft lights are drawn (flyscene.cpp:529-538 uses rand())
 //            [--dump-rays PREFIX]            camera origin + per-pixel primary directions (no GPU)
 //            [--ppm-from-f32 IN.f32 OUT.ppm] W*H*3 floats -> the reference's ASCII P3 (no GPU)
@@ -83,7 +84,7 @@ int main(int argc, char **argv) {
   bool seeded = false;
   int W = 1000, H = 1000, depth = 2, device = -1;  // main.cpp:8-9 window size, flyscene.hpp:142
   float fovy = 60.f;
-  bool has_view = false, nolights = false, load_only = false;
+  bool has_view = false, nolights = false, load_only = false, lights_only = false;
   int gpus = 1;
   float view[12];
   std::vector<std::array<float, 6>> lights, dirlights;
@@ -102,6 +103,7 @@ int main(int argc, char **argv) {
     else if (a == "--png-from-u8") { need(i, 2); u8_in = argv[++i]; u8_out = argv[++i]; }
     else if (a == "--seed") { need(i, 1); seed = strtoull(argv[++i], nullptr, 10); seeded = true; }
     else if (a == "--dump-lights") { need(i, 1); lights_prefix = argv[++i]; }
+    else if (a == "--lights-only") lights_only = true;
     else if (a == "--dump-scene") { need(i, 1); dump_prefix = argv[++i]; }
     else if (a == "--dump-scene-noboxes") { need(i, 1); dump_prefix = argv[++i]; load_only = true; }
     else if (a == "--gpus") { need(i, 1); gpus = atoi(argv[++i]); }
@@ -144,8 +146,8 @@ int main(int argc, char **argv) {
   flyscene->DEVICE = device;
   flyscene->DEVICES = gpus;
   flyscene->max_depth = depth;
-  flyscene->initialize(W, H);
-  if (!flyscene->ok()) { fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str()); return 1; }
+  if (!lights_only) flyscene->initialize(W, H);
+  if (!lights_only && !flyscene->ok()) { fprintf(stderr, "raytrace: %s\n", flyscene->lastError().c_str()); return 1; }
   flyscene->getCamera()->setPerspectiveMatrix(fovy, W / (float)H, 0.1f, 100.0f);
   if (has_view) {
     Eigen::Affine3f v;
@@ -167,6 +169,10 @@ int main(int argc, char **argv) {
     std::vector<float> lf;
     for (auto &l : flyscene->lights) { for (int c = 0; c < 3; ++c) lf.push_back(l.first[c]); for (int c = 0; c < 3; ++c) lf.push_back(l.second[c]); }
     dump(lights_prefix + ".lights.f32", lf);
+  }
+  if (lights_only) {  // --dump-lights without a scene or a device (CPU tests of Flyscene::sphericalLight)
+    delete flyscene;
+    return 0;
   }
   flyscene->OUTPUT_BINARY_NAME = out_p6;
   flyscene->OUTPUT_PNG_NAME = out_png;

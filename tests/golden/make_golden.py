@@ -49,6 +49,29 @@ CASES = [
 ]
 
 
+# Soft lights: name, model, w, h, view, max_depth, srand seed, soft lights (x y z r g b radius n).
+# The light list is drawn by the reference's own Flyscene::sphericalLight with libc rand() after srand(seed), then the
+# light itself is appended with rgb / (n + 1) as the "s" branch of its addLight does: n + 1 point lights per entry.
+SOFT_CASES = [
+    ("soft17_dodge", "dodgeColorTest.obj", 64, 48, rotview(2.1, -0.3, [0.05, 0.1, -1.5]), 2, 7,
+     [[-0.5, 2.0, 3.0, 0.9, 0.8, 0.7, 0.35, 16]]),                                               # L = 17
+    ("soft65_testding", "testding.obj", 48, 48, rotview(-0.3, 0.2, [0, 0, -1.8]), 2, 11,
+     [[1.0, 1.5, 2.0, 1.0, 1.0, 1.0, 0.5, 40], [-1.5, 2.0, 1.0, 0.6, 0.7, 0.9, 0.25, 23]]),       # L = 41 + 24 = 65
+]
+
+
+def main_soft():
+    for name, model, w, h, view, md, seed, soft in SOFT_CASES:
+        r = po.ref_run(po.ref_model(model), w, h, view=view, max_depth=md, soft=soft, srand=seed, procs=os.cpu_count() or 1,
+                       dump_scene=True)
+        np.savez_compressed(os.path.join(HERE, "case_" + name + ".npz"), model=model, w=w, h=h, view=view, max_depth=md,
+                            srand=seed, soft=np.asarray(soft, np.float32), point_lights=r["lights"],
+                            dir_lights=np.zeros((0, 6), np.float32), rgb=r["rgb"], hit=r["hit"], t=r["t"], dir=r["dir"],
+                            camera=r["camera"],
+                            counts=np.array([r["counts"][k] for k in ("primary", "shadow", "reflection", "hits")], np.int64))
+        print(name, "lights", len(r["lights"]), "hits", int((r["hit"] >= 0).sum()), "shadow rays", r["counts"]["shadow"])
+
+
 def main():
     meshes = {}
     for name, model, w, h, view, md, pl, dl in CASES:
@@ -73,4 +96,6 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--soft-only" not in sys.argv:
+        main()
+    main_soft()

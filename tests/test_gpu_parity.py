@@ -231,3 +231,42 @@ def test_tie_heavy_random_scenes_match_the_oracle(rtp, po, seed):
         assert [st["rays_primary"], st["rays_shadow"], st["rays_reflection"], st["hits"]] == \
                [o["counts"][k] for k in ("primary", "shadow", "reflection", "hits")]
     s.close()
+
+
+def test_shadow_ray_count_beyond_32_bits_is_refused(rtp):
+    """shadow rays of a level are indexed (pixel, light) in 32 bits.  A frame whose pixels x lights would
+    overflow must be refused with an error, not traced with a wrapped count."""
+    m = load_golden_mesh("plane")
+    s = make_scene(rtp, m)
+    lights = np.tile(np.float32([[0.1, 2.0, 3.0, 0.001, 0.001, 0.001]]), (1100, 1))
+    lights[:, 0] += np.arange(1100, dtype=np.float32) * 1e-3
+    s.set_lights(lights, None)
+    s.set_camera(1920, 1080)
+    with pytest.raises(rtp.RtpError, match="shadow rays"):      # 2 088 960 tile-padded pixels x 1100 lights > 2^31
+        s.render(1920, 1080, max_depth=1, want=("rgb8",))
+    s.set_camera(64, 64)
+    out = s.render(64, 64, max_depth=1, want=("hit",))            # the same 1100 lights on a small frame are fine
+    assert out["stats"]["rays_shadow"] == out["stats"]["hits"] * 1100 and out["stats"]["hits"] > 0
+    s.close()
+
+
+@pytest.mark.parametrize("seed,dist", [(0, 300.0), (1, 3000.0), (2, 40000.0)])
+def test_far_camera_matches_the_oracle(rtp, po, seed, dist):
+    """P = o + t*d carries ulp(|o|) of rounding, which grows with the camera distance while the build-time
+    padding of the hierarchy does not.  rtp_set_camera widens the boxes for far cameras (ensure_pad); primary ids and
+    colours must still be the oracle's, which tests every face."""
+    m = soup(po, 100 + seed, n_tris=300)
+    s = make_scene(rtp, m, with_boxes=True)
+    s.set_lights(SOUP_LIGHTS, None)
+    w, h = 64, 48
+    fovy = float(np.degrees(2 * np.arctan(1.6 / dist)))          # narrow lens: the scene still fills the frame
+    for axis in range(3):
+        view = np.zeros((3, 4), np.float32)
+        view[:, :3] = np.roll(np.eye(3, dtype=np.float32), axis, axis=1)
+        view[2, 3] = -dist
+        s.set_camera(w, h, view.ravel(), fovy=fovy)
+        out = s.render(w, h, max_depth=2)
+        o = po.render(m, w, h, view=view.ravel(), fovy=fovy, max_depth=2, point_lights=SOUP_LIGHTS)
+        assert (o["hit"] >= 0).mean() > 0.05
+        check_image(out["rgb"].reshape(-1, 3), out["hit"].ravel(), o["rgb"], o["hit"], exact_fraction=0.5)
+    s.close()

@@ -99,31 +99,43 @@ def test_c4_shape_instanced_deep_bounces(rtp, po):
     assert out["stats"]["rays_reflection"] > 0
 
 
-def test_c5_shape_ambient_occlusion_rays(rtp, po):
-    """BASELINE config 5 shape: from primary hit points on the 1 M-triangle terrain, 64 random
-    hemisphere directions each through the any-hit entry point (= Flyscene::shadow)."""
+def test_c5_ambient_occlusion_rays_as_defined(rtp, po):
+    """BASELINE config 5 as SURVEY.md 8(d) defines it, with the generator bench.py --workload c5 uses
+    (synth.ao_rays_pixels): from the primary hit point P of a pixel of the 1920x1080 C3 frame, moved 0.003 along the
+    interpolated normal, 64 directions uniform on the hemisphere around that normal from Philox4x32-10 keyed by
+    (seed 1234, pixel index) - through the any-hit entry point (= Flyscene::shadow).  The oracle traces the same rays."""
+    import torch
     synth = synth_mod()
     m = synth.terrain(708)
     view = synth.look_at((0.0, 0.30, 0.20), (0.0, -0.05, -0.08))
-    w, h = 192, 108
+    w, h = 1920, 1080
     s = rtp_scene(rtp, m)
     s.set_lights(synth.LIGHT_DEFAULT, None)
     s.set_camera(w, h, view)
-    cam = po.camera_derive(w, h, view=view)
     pm = po_mesh(po, m)
     rng = np.random.default_rng(5)
-    idx = rng.choice(w * h, size=400, replace=False)
+    idx = np.sort(rng.choice(w * h, size=400, replace=False))
     px = np.stack([idx % w, idx // w], 1).astype(np.int32)
     o = po.render(pm, w, h, view=view, max_depth=1, point_lights=synth.LIGHT_DEFAULT, pixels=px, threads=16)
     keep = o["hit"] >= 0
-    eye = np.asarray(cam[0], np.float32)
-    P = eye[None, :] + o["t"][keep, None] * o["dir"][keep]
-    f = np.asarray(m["faces"])[o["hit"][keep]]
-    V = (np.asarray(m["verts"])[:, :3] * np.float32(m["shape"][0]) + np.asarray(m["shape"], np.float32).reshape(3, 4)[:, 3]).astype(np.float32)
-    n = np.cross(V[f[:, 1]] - V[f[:, 0]], V[f[:, 2]] - V[f[:, 0]])
-    n /= np.linalg.norm(n, axis=1, keepdims=True)
-    n = np.where((n * (eye[None, :] - P)).sum(1, keepdims=True) < 0, -n, n).astype(np.float32)
-    rays = synth.ao_rays(P.astype(np.float32), n, n_per_point=64)
+    assert keep.mean() > 0.8
+    # the bench's own workload generation (camera_rays + plane intersection) finds these hit points
+    eye, dirs = synth.camera_rays(w, h, view)
+    P = synth.primary_hit_points(m, o["hit"][keep], eye, dirs[idx[keep]])
+    P_oracle = eye[None, :] + o["t"][keep, None] * o["dir"][keep]
+    assert np.abs(P - P_oracle).max() < 1e-4
+    N = synth.shading_normals(m, o["hit"][keep], P)
+    assert (N[:, 1] > 0.2).all()  # a height field seen from above: shading normals point up
+    pix = idx[keep].astype(np.int64)
+    rays = synth.ao_rays_pixels(P, N, pix, n_per_point=64)
+    # device generation (torch, what bench.py runs) = host generation (numpy), bit for bit
+    dev = torch.device("cuda", 0)
+    rays_dev = synth.ao_rays_pixels(torch.from_numpy(P).to(dev), torch.from_numpy(N).to(dev), torch.from_numpy(pix).to(dev),
+                                    n_per_point=64, xp=torch)
+    assert np.array_equal(rays_dev.cpu().numpy().view(np.uint32), rays.view(np.uint32))
+    # keyed by pixel: any subset / order of the pixels draws the same rays for them
+    half = synth.ao_rays_pixels(P[::2], N[::2], pix[::2], n_per_point=64)
+    assert np.array_equal(half.reshape(-1, 64, 6), rays.reshape(-1, 64, 6)[::2])
     got = s.trace_rays(rays, rtp.RAYS_ANYHIT)["occluded"].astype(np.int32)
     ref = po.shadow_rays(pm, rays, threads=16)
     assert np.array_equal(got, ref), f"{(got != ref).sum()} of {len(rays)} AO rays differ"
@@ -152,3 +164,53 @@ def test_c3_gpu_built_bvh_equals_host_built(rtp):
         s.close()
     assert np.array_equal(frames[0]["hit"], frames[1]["hit"])
     assert bits_equal(frames[0]["rgb"], frames[1]["rgb"]).all()
+
+
+def test_c4_full_size_10m_triangles_4k_depth6(rtp, po):
+    """BASELINE config 4 AT ITS STATED SIZE: dodgeColorTest.obj instanced 25 x 25 = 10 194 375
+    triangles, 3840x2160, 4 lights, max_depth 6 (reflection depth 5) - the bench.py --workload c4 frame.
+    8192 random pixels against the oracle (which tests all 52 970 BoundingBoxes per ray); the frame of the device-built
+    hierarchy and the frame assembled from 8 ranks (rtp_scene_create_multi; the ranks share the GPUs present) must be
+    the host-SAH single-device frame bit for bit.  Pins the deep tree (stack bound), the parked-ray list under 8.3 M
+    paths and 32-bit indexing at 10 M triangles / 33 M shadow-ray slots."""
+    synth = synth_mod()
+    g = load_golden_mesh("dodgeColorTest")
+    base = dict(verts=g.verts, normals=g.normals, faces=g.faces, face_mat=g.face_mat, materials=g.materials, shape=g.shape)
+    m = synth.instanced(base, 25, 25)
+    assert len(m["faces"]) == 10194375
+    view = synth.look_at((0.55, 0.45, 0.7), (0.0, -0.1, 0.0))  # the bench.py camera
+    w, h, depth = 3840, 2160, 6
+    pm = po_mesh(po, m)
+    rng = np.random.default_rng(44)
+    idx = rng.choice(w * h, size=8192, replace=False)
+    px = np.stack([idx % w, idx // w], 1).astype(np.int32)
+    o = po.render(pm, w, h, view=view, max_depth=depth, point_lights=synth.LIGHTS_C2, pixels=px, threads=16)
+    assert (o["hit"] >= 0).mean() > 0.2 and o["counts"]["reflection"] > 1000
+
+    def frame(**kw):
+        s = rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], **kw)
+        s.set_lights(synth.LIGHTS_C2, None)
+        s.set_camera(w, h, view)
+        out = s.render(w, h, max_depth=depth, want=("rgb", "hit"))
+        info = s.info()
+        if "devices" not in kw:  # the library's splitter built the oracle's BoundingBox list (52 970 boxes)
+            bb, off, bf = s.boxes()
+            assert np.array_equal(off, pm.box_off) and np.array_equal(bf, pm.box_faces) and bits_equal(bb, pm.boxes).all()
+        s.close()
+        return out, info
+
+    ref, info = frame(build=rtp.BUILD_HOST_SAH)
+    assert info["n_triangles"] == 10194375
+    compare(ref, o, px)
+    st = ref["stats"]
+    assert st["rays_primary"] == w * h and st["rays_shadow"] == 4 * st["hits"] and st["rays_reflection"] > 0
+    total = st["rays_primary"] + st["rays_shadow"] + st["rays_reflection"]
+    assert total > 25_000_000
+    lbvh, _ = frame(build=rtp.BUILD_GPU_LBVH)
+    assert np.array_equal(lbvh["hit"], ref["hit"]) and bits_equal(lbvh["rgb"], ref["rgb"]).all()
+    del lbvh
+    ndev = rtp.device_count()
+    multi, _ = frame(devices=[r % ndev for r in range(8)])
+    assert np.array_equal(multi["hit"], ref["hit"]) and bits_equal(multi["rgb"], ref["rgb"]).all()
+    for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits"):
+        assert multi["stats"][k] == st[k], k

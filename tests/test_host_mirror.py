@@ -168,6 +168,49 @@ def test_flyscene_soft_light_and_single_ray_api(tmp_path):
     assert (w, h) == (40, 40) and got.min() >= 0 and got.max() <= 255
 
 
+SOFT_CASES = ["soft17_dodge", "soft65_testding"]
+
+
+def soft_args(c):
+    a = ["--srand", str(int(c["srand"])), "--nolights"]
+    for l in c["soft"]:
+        a += ["--soft"] + [repr(float(x)) for x in l[:7]] + [str(int(l[7]))]
+    return a
+
+
+@pytest.mark.parametrize("case", SOFT_CASES)
+def test_spherical_light_list_equals_the_reference(case, tmp_path):
+    """Flyscene::sphericalLight (flyscene.cpp:529-538) + the "s" branch of addLight (:213-237): after the same srand() the
+    mirror class draws the light list the UNMODIFIED reference drew (fixture: ref_harness calling the reference's own
+    sphericalLight) - positions and colours bit for bit, in order.  No GPU needed."""
+    need_cli()
+    c = load_case(case)
+    pre = str(tmp_path / "l")
+    r = subprocess.run([CLI, "--lights-only", "--dump-lights", pre] + soft_args(c), capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    got = np.fromfile(pre + ".lights.f32", np.float32).reshape(-1, 6)
+    want = np.asarray(c["point_lights"], np.float32)
+    assert got.shape == want.shape and len(got) == sum(int(l[7]) + 1 for l in c["soft"])
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", SOFT_CASES)
+def test_soft_light_frame_equals_the_reference_image(case, tmp_path):
+    """17 and 65 point lights drawn by sphericalLight: result.ppm of the drop-in equals the reference's pixels."""
+    need_cli()
+    c = load_case(case)
+    out = str(tmp_path / "result.ppm")
+    model = str(c["model"]).replace(".obj", "")
+    cmd = [CLI, "--model", model_path(model), "--size", str(int(c["w"])), str(int(c["h"])), "--depth", str(int(c["max_depth"])),
+           "--out", out, "--view"] + [repr(float(x)) for x in c["view"]] + soft_args(c)
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    w, h, got = ppm_values(out)
+    diff = np.abs(got - expected_ppm(c))
+    assert (diff > 1).any(axis=2).mean() <= 1e-3 and (diff > 0).any(axis=2).mean() <= 1e-3
+
+
 DUMPS = ["verts.f32", "normals.f32", "faces.i32", "fmat.i32", "materials.f32", "shape.f32", "fnormal.f32", "boxes.f32",
          "box_off.i32", "box_faces.i32"]
 
