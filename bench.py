@@ -84,6 +84,62 @@ def build_workload(name, synth):
     raise SystemExit(f"unknown workload {name}")
 
 
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def roofline_dict(workload, kernel, kernel_ms, rays, n_tris, sm_count, clocks, peaks, extra=None, alg_extra=0):
+    """The line's `roofline` for the dominant kernel.
+
+    Primary bound = ISSUE RATE: the traversal kernels are bound by warp-instruction issue under divergence, not by HBM
+    (measured DRAM traffic is ~5 % of the algorithmic bytes: neighbouring rays share nodes through L1/L2).
+      achieved = warp instructions of the launch (ncu smsp__inst_executed.sum, profiles/traffic.json, scaled to this
+                 launch's ray count) / its CUDA-event duration measured live here;
+      peak     = SMs x 4 schedulers x SM clock (one warp instruction per scheduler per cycle), clock = median under load.
+    `lane_efficiency` (ncu thread_inst / inst / 32) says how many of those slots carry a live lane; `dram_frac` is the
+    measured DRAM traffic over the same duration against MEASURED_PEAKS.json hbm_gbs.
+    `contract` keeps SURVEY.md 8(d)'s HBM figure (algorithmic bytes per ray x rays / time / hbm peak): it exceeds 1 for
+    coherent rays because the caches serve most of those bytes - it is reported, it does not bound the kernel."""
+    hbm = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)"
+    alg = b_alg(n_tris) + alg_extra
+    sec = kernel_ms / 1e3 if kernel_ms > 0 else float("inf")
+    contract = dict(bound="hbm", achieved=rays * alg / sec / 1e9, peak=hbm, unit="GB/s", frac=rays * alg / sec / 1e9 / hbm,
+                    alg_bytes_per_ray=alg, peak_source=peak_src,
+                    note="SURVEY.md 8(d) definition; not a bound for this kernel (see roofline.dram_frac)")
+    sm_clock = float((clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6
+    issue_peak = sm_count * 4 * sm_clock
+    ent = None
+    try:
+        ent = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(workload, {}).get(kernel)
+    except Exception:
+        pass
+    if not isinstance(ent, dict):
+        ent = None
+    r = dict(bound="issue", unit="Gwarp-inst/s", peak=issue_peak / 1e9, kernel=kernel, kernel_ms=kernel_ms,
+             rays_per_launch_set=rays, grays_per_s_kernel=rays / sec / 1e9,
+             peak_source=f"{sm_count} SMs x 4 schedulers x {sm_clock / 1e6:.0f} MHz (median SM clock under load)")
+    if ent and ent.get("warp_inst") and ent.get("rays"):
+        scale = rays / float(ent["rays"])
+        winst = ent["warp_inst"] * scale
+        traffic = ent["dram_bytes"] * scale
+        r.update(achieved=winst / sec / 1e9, frac=winst / sec / issue_peak, traffic=traffic,
+                 warp_inst_per_launch=winst, lane_efficiency=ent["lanes"] / 32.0,
+                 useful_lane_frac=winst / sec / issue_peak * ent["lanes"] / 32.0,
+                 dram_gbs=traffic / sec / 1e9, dram_frac=traffic / sec / 1e9 / hbm, dram_peak_source=peak_src,
+                 traffic_bytes_per_ray=traffic / rays if rays else None,
+                 counters_from=ent.get("from", "profiles/traffic.json") + (f"; scaled x{scale:.4f} to this launch's rays" if abs(scale - 1) > 1e-3 else ""))
+    else:
+        r.update(achieved=None, frac=None, traffic=None, note="no ncu capture of this kernel for this workload in profiles/traffic.json")
+    r["contract"] = contract
+    if extra:
+        r.update(extra)
+    return r
+
+
 class ClockSampler:
     """SM clock and throttle reasons DURING the timed region (B200_PROFILING.md).  Sampled in-process
     through NVML every few ms (the timed region of the default run is well under a second, too short
@@ -301,6 +357,8 @@ def run_ours(args, wl, rtp):
     for _ in range(args.steps):
         flush.zero_()          # evict the scene from L2 between timed iterations (untimed)
         sync_all()
+        if peer:
+            mg.align_start(scene, img, stream)  # N > 1: all GPUs leave the start line together (device-side, untimed)
         ev0.record()
         step()
         ev1.record()
@@ -382,35 +440,19 @@ def run_ours(args, wl, rtp):
         total_ms = sum(ms_steps)
         value = rays_frame * args.steps / (total_ms / 1e3) / 1e6
         e2e_val = rays_frame * len(e2e_ms) / (sum(e2e_ms) / 1e3) / 1e6
-        # roofline of the dominant kernel (rank 0's launches; algorithmic bytes from SURVEY.md 8d)
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        # roofline of the dominant kernel (rank 0's launches)
+        peaks = load_peaks()
         n_tris = info["n_triangles"]
         mc, ms_, mo = float(np.mean(k_closest)), float(np.mean(k_any)), float(np.mean(k_shade))
         own = float(st["rays_primary"] + st["rays_reflection"]), float(st["rays_shadow"])
         dom = "k_trace<closest>" if mc >= ms_ else "k_trace<anyhit>"
         dom_ms, dom_rays = (mc, own[0]) if mc >= ms_ else (ms_, own[1])
-        achieved = dom_rays * b_alg(n_tris) / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
-        traffic, winst = None, None
-        try:
-            tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-            traffic = tj.get(args.workload, {}).get(dom)
-            winst = tj.get(args.workload + "_warp_instructions", {}).get(dom)
-        except Exception:
-            pass
-        # issue-rate cross-check: warp instructions of the dominant launch (ncu capture) over its
-        # live duration, against SMs x 4 schedulers x SM clock
-        sm_clock = float((clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0) * 1e6
-        issue_peak = torch.cuda.get_device_properties(local).multi_processor_count * 4 * sm_clock
-        issue = dict(note="traversal is issue/latency bound, not DRAM bound: see profiles/",
-                     grays_per_s_kernel=dom_rays / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0)
-        if winst and dom_ms > 0:
-            issue.update(warp_inst_per_launch=winst, achieved_warp_inst_per_s=winst / (dom_ms / 1e3),
-                         peak_warp_inst_per_s=issue_peak, frac=winst / (dom_ms / 1e3) / issue_peak)
+        roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, n_tris, torch.cuda.get_device_properties(local).multi_processor_count,
+                             clocks, peaks,
+                             extra=dict(kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
+                                        kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events on the launch "
+                                                        f"stream, the frame as one tile group (each kernel alone on the GPU, k_coop counted with its "
+                                                        f"k_trace), {float(np.mean(ms_serial)):.4f} ms per step"))
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                     ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
                     dtype="f32", data="synthetic",
@@ -424,6 +466,9 @@ def run_ours(args, wl, rtp):
                                 peer_image_equals_nccl_gather=same,
                                 tile_groups=f"{groups} bands of this rank's tiles, each on its own CUDA stream",
                                 l2="256 MiB memset between timed steps (untimed) flushes the 126 MB L2",
+                                timed_region="per step: host barrier + device sync, then on every GPU [start-line kernel (N > 1, untimed): "
+                                             "waits until all GPUs are there] - start event - frame (+ frame barrier on N > 1) - end event; "
+                                             "max over ranks of the event time",
                                 scene_build_s=round(t_build, 2)),
                     clocks=clocks,
                     e2e=dict(value=e2e_val, unit=UNIT, h2d_bytes_per_step=cam_bytes, d2h_bytes_per_step=w * h * 3,
@@ -432,14 +477,7 @@ def run_ours(args, wl, rtp):
                                   "set lights/camera + tile render into GPU 0's image + D2H of the uint8 image on rank 0",
                              pipelined=pipe),
                     gpu_launches=launches_rank0,
-                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak,
-                                  traffic=traffic, kernel=dom, kernel_ms=dom_ms, rays_per_launch_set=dom_rays,
-                                  alg_bytes_per_ray=b_alg(n_tris),
-                                  peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
-                                  kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
-                                  kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events, the frame as "
-                                                  f"one tile group (each kernel alone on the GPU), {float(np.mean(ms_serial)):.4f} ms per step",
-                                  issue=issue))
+                    roofline=roof)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_port(wl)
         print(json.dumps(line))
@@ -449,6 +487,99 @@ def run_ours(args, wl, rtp):
     scene.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_multi_device(args, wl, rtp):
+    """`python bench.py --gpus N` WITHOUT torchrun: one process, N GPUs, through the drop-in's own multi-GPU entry point
+    (rtp_scene_create_multi + rtp_render = Flyscene::DEVICES / `raytrace --gpus N`): one host thread and one stream per
+    GPU inside the library, every GPU's resolve kernel storing its tiles into GPU 0's image, fork / join by CUDA events.
+    `value` = rays of the frame / device time of the whole frame on GPU 0's stream (its end event follows the join with
+    every other GPU); `e2e` = the same call by wall clock, image in host memory."""
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the hot path is CUDA only (no CPU fallback)")
+    n = args.gpus
+    ndev = rtp.device_count()
+    devices = [r % ndev for r in range(n)]
+    m, w, h, md = wl["mesh"], wl["w"], wl["h"], wl["max_depth"]
+    t0 = time.perf_counter()
+    scene = rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], devices=devices)
+    t_build = time.perf_counter() - t0
+    one = rtp.Scene(m["verts"], m["normals"], m["faces"], m["face_mat"], m["materials"], m["shape"], device=0)
+    for sc in (scene, one):
+        sc.set_lights(wl["lights"], None)
+        sc.set_camera(w, h, wl["view"])
+    info = scene.info()
+    host = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory()
+    host1 = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory()
+    one.render(w, h, max_depth=md, want=("rgb8",), out={"rgb8": host1.numpy().reshape(h, w, 3)})
+    one.close()
+    flushes = [torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", d)) for d in sorted(set(devices))]
+
+    def sync_all():
+        for d in sorted(set(devices)):
+            torch.cuda.synchronize(d)
+
+    def frame(flags=0):
+        return scene.render(w, h, max_depth=md, want=("rgb8",), out={"rgb8": host.numpy().reshape(h, w, 3)}, flags=flags)["stats"]
+
+    sampler = ClockSampler(devices[0])
+    sampler.start()
+    for _ in range(max(args.warmup, 3)):
+        st = frame()
+    same = bool(torch.equal(host, host1))
+    if not same:
+        raise SystemExit("bench.py: the multi-device image differs from the one-device image")
+    rays_frame = st["rays_primary"] + st["rays_shadow"] + st["rays_reflection"]
+    t_begin = time.perf_counter()
+    ms_steps, e2e_ms = [], []
+    for _ in range(args.steps):
+        for f in flushes:
+            f.zero_()
+        sync_all()
+        t0 = time.perf_counter()
+        scene.set_lights(wl["lights"], None)
+        scene.set_camera(w, h, wl["view"])
+        st = frame()
+        e2e_ms.append(1e3 * (time.perf_counter() - t0))
+        ms_steps.append(st["ms_trace"])
+    clocks = sampler.stop(t_begin, time.perf_counter())
+    k_closest, k_any, k_shade = [], [], []
+    for _ in range(min(args.steps, 20)):
+        for f in flushes:
+            f.zero_()
+        sync_all()
+        ps = frame(flags=rtp.RENDER_PROFILE)
+        k_closest.append(ps["ms_closest"]); k_any.append(ps["ms_anyhit"]); k_shade.append(ps["ms_shade"])
+    total_ms = sum(ms_steps)
+    peaks = load_peaks()
+    mc, ms_, mo = float(np.mean(k_closest)), float(np.mean(k_any)), float(np.mean(k_shade))
+    dom = "k_trace<closest>" if mc >= ms_ else "k_trace<anyhit>"
+    dom_ms = max(mc, ms_)
+    dom_rays = float(st["rays_primary"] + st["rays_reflection"] if mc >= ms_ else st["rays_shadow"]) / n
+    roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, info["n_triangles"],
+                         torch.cuda.get_device_properties(devices[0]).multi_processor_count, clocks, peaks,
+                         extra=dict(kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
+                                    kernels_ms_from="more steps with RTP_RENDER_PROFILE: per-kernel CUDA events, max over the devices; "
+                                                    "rays_per_launch_set = the frame's rays of that kind / devices"))
+    cam_bytes = 4 * (12 + 4 + 2) + 24 * len(wl["lights"])
+    line = dict(metric=METRIC, value=rays_frame * args.steps / (total_ms / 1e3) / 1e6, unit=UNIT, n_gpus=n, steps=args.steps,
+                warmup=max(args.warmup, 3), ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong",
+                vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=wl["desc"], rays_per_frame=rays_frame, triangles=info["n_triangles"], bvh_nodes=info["n_bvh_nodes"],
+                            parallelism=f"tile{n}, ONE process: rtp_scene_create_multi on devices {devices}",
+                            gather="every device's resolve kernel stores its tiles into device 0's image (peer access), join by CUDA events",
+                            multi_device_image_equals_one_device=same,
+                            l2="256 MiB memset per device between timed steps (untimed)", scene_build_s=round(t_build, 2),
+                            timed_region="CUDA events on device 0's stream around the frame: fork event - all devices' kernels - join; "
+                                         "rtp_stats.ms_trace of rtp_render"),
+                clocks=clocks,
+                e2e=dict(value=rays_frame * len(e2e_ms) / (sum(e2e_ms) / 1e3) / 1e6, unit=UNIT, h2d_bytes_per_step=cam_bytes,
+                         d2h_bytes_per_step=w * h * 3, ms_per_step=float(np.mean(e2e_ms)),
+                         what="rtp_set_lights + rtp_set_camera + rtp_render (multi-device scene) -> host uint8 image, wall clock"),
+                gpu_launches=int(st["kernel_launches"]) * args.steps, roofline=roof)
+    print(json.dumps(line))
+    scene.close()
 
 
 def run_c5(args, wl, rtp):
@@ -540,6 +671,13 @@ def run_c5(args, wl, rtp):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_steps.append(float(t.item()))
     clocks = sampler.stop(t_begin, time.perf_counter()) if rank == 0 else None
+    k_list = []  # the trace kernel alone (this rank's launch), by the library's CUDA events on the launch stream
+    for _ in range(3):
+        flush.zero_()
+        sync_all()
+        k_list.append(scene.trace_rays_device(rays.data_ptr(), n_rays, rtp.RAYS_ANYHIT, d_occ=occ.data_ptr(), stream=stream,
+                                              want_stats=True)["ms_trace"])
+    k_ms = float(np.mean(k_list))
     # end to end: rays from pinned host memory, occlusion flags back to the host (a bounded slice: the full list is 3 GB)
     n_e2e = min(n_rays, 8 << 20)
     h_rays = rays[:n_e2e].cpu().pin_memory()
@@ -558,15 +696,12 @@ def run_c5(args, wl, rtp):
     if rank == 0:
         total_ms = sum(ms_steps)
         value = rays_step * args.steps / (total_ms / 1e3) / 1e6
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+        peaks = load_peaks()
         n_tris = info["n_triangles"]
-        k_ms = total_ms / args.steps  # the any-hit trace kernel is >99% of the step
-        achieved = n_rays * b_alg(n_tris) / (k_ms / 1e3) / 1e9
+        roof = roofline_dict("c5", "k_trace<RaysAny>", k_ms, float(n_rays), n_tris, torch.cuda.get_device_properties(local).multi_processor_count,
+                             clocks, peaks, alg_extra=24,
+                             extra=dict(kernel_ms_from="3 more steps timed by the library's CUDA events around the trace launch alone "
+                                                       "(rtp_trace_rays_device with statistics), L2 flushed before each"))
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                     ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
                     dtype="f32", data="synthetic",
@@ -579,11 +714,7 @@ def run_c5(args, wl, rtp):
                              h2d_bytes_per_step=n_e2e * 24, d2h_bytes_per_step=n_e2e, ms_per_step=float(np.mean(e2e_ms)),
                              what=f"{n_e2e} rays per GPU from pinned host memory -> rtp_trace_rays_device(any-hit) -> occlusion bytes to the host"),
                     gpu_launches=args.steps,
-                    roofline=dict(bound="hbm", achieved=achieved, peak=peak, unit="GB/s", frac=achieved / peak, traffic=None,
-                                  kernel="k_trace<RaysAny>", kernel_ms=k_ms, rays_per_launch_set=float(n_rays),
-                                  alg_bytes_per_ray=b_alg(n_tris) + 24,
-                                  peak_source="MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s",
-                                  note="kernel_ms = step time (the trace kernel plus the per-pixel sum / gather)"))
+                    roofline=roof)
         print(json.dumps(line))
     scene.close()
     if world > 1:
@@ -609,6 +740,8 @@ def main():
         run_reference(args, wl, synth)
     elif args.workload == "c5":
         run_c5(args, wl, rtp)
+    elif args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        run_multi_device(args, wl, rtp)  # one process, N devices: the C++ multi-GPU path of the drop-in
     else:
         run_ours(args, wl, rtp)
 

@@ -101,7 +101,9 @@ typedef struct rtp_stats {
   /* with RTP_RENDER_PROFILE: summed device time per kernel kind */
   float ms_closest; /* closest-hit traversal (calculateMinimumFace)                            */
   float ms_anyhit;  /* shadow-ray traversal (shadow)                                           */
-  float ms_shade;   /* streaming kernels: ray generation, hit preparation, Phong, resolve      */
+  float ms_shade;   /* streaming kernels: Phong + reflection spawn of the camera level, resolve + image   */
+  float ms_paths;   /* bounce levels >= 1, path by path in one persistent kernel (traceRay's recursion) */
+  int32_t reserved;
 } rtp_stats;
 
 /* ---- lifetime ---------------------------------------------------------------------------- */

@@ -149,6 +149,9 @@ struct rtp_scene {
   DevBuf<int> park;  // parked-ray list of the trace kernels
   int *barrier_timeouts = nullptr;      // [1] waits of rtp_peer_barrier that gave up: page-locked, mapped - the kernel
   int *barrier_timeouts_dev = nullptr;  // writes it through the device alias, the host reads it without a device sync
+  int paths_from = 1;      // first bounce level k_paths takes over (levels below it run as per-level launches)
+  int deep_mode = -1;      // bounce levels >= 1: 1 = k_paths, 0 = per-level kernels, -1 = by frame size (RTP_DEEP, at scene creation)
+  int paths_px_big = 2600000, paths_px_small = 1100000;  // -1: k_paths up to this many pixels per rank (scene larger / not larger than the L2)
   float pad_cur = 0.f;  // padding of the hierarchy's boxes right now (build-time pad, grown by ensure_pad)
   // multi-device scene (rtp_scene_create_multi): this is device 0's scene, peers[r - 1] the replica of rank r
   std::vector<rtp_scene *> peers;
@@ -241,6 +244,10 @@ int init_device_side(rtp_scene *s) {
   CK(cudaEventCreateWithFlags(&s->frame_start, cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&s->frame_done, cudaEventDisableTiming));
   if (const char *te = std::getenv("RTP_TIMELINE")) s->timeline = std::atoi(te);
+  if (const char *de = std::getenv("RTP_DEEP")) s->deep_mode = std::string(de) == "wavefront" ? 0 : std::string(de) == "paths" ? 1 : -1;  // per scene
+  if (const char *te = std::getenv("RTP_PATHS_PX_BIG")) s->paths_px_big = std::atoi(te);
+  if (const char *te = std::getenv("RTP_PATHS_PX_SMALL")) s->paths_px_small = std::atoi(te);
+  if (const char *pe = std::getenv("RTP_PATHS_FROM")) s->paths_from = std::atoi(pe);
   if (const char *ge = std::getenv("RTP_GROUPS")) s->groups = std::min(std::max(std::atoi(ge), 0), kMaxGroups);
   return RTP_OK;
 }
@@ -405,6 +412,12 @@ int rtp_scene_create_multi(const rtp_mesh *mesh, const int *devices, int n_devic
     return fail(RTP_ERR_INVALID, msg);
   }
   HostScene &h = s->host;
+#ifdef RTP_SMEM_STACK
+  if (!gpu_build && h.bvh_depth >= RTP_SMEM_STACK - 2) {
+    delete s;
+    return fail(RTP_ERR_INVALID, "RTP_SMEM_STACK experiment build: the hierarchy is deeper than the shared-memory stack");
+  }
+#endif
   int rc = RTP_OK;
   {
     DeviceGuard g(dev[0]);
@@ -751,12 +764,23 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   // launches are issued phase by phase across the groups, so that the groups advance together
   if (p.user_rays)  // caller-supplied rays go through the ray list; camera rays are generated inside the trace kernel
     for (int g = 0; g < G; ++g) { CK(mark(2)); launch_raygen(gp[g], gs[g]); ++n; CK(stamp("raygen", g, 0, gs[g])); }
-  for (int d = 0; d < p.max_depth; ++d) {
+  // below the camera level the bounce levels run path by path in one persistent kernel (k_paths) instead of three
+  // dependent launches per level; RTP_DEEP=wavefront keeps the per-level kernels (A/B runs, parity suite)
+  // Which of the two runs the levels below the camera level - measured on B200 (profiles/r02_paths.md): the per-level
+  // kernels keep neighbouring paths together and win on big frames, k_paths has no per-level latency floor and wins
+  // once a rank's share is small (frame ms, per-level / k_paths: C4 8.3 M px 4.32 / 5.04, 2.1 M px 2.15 / 1.89,
+  // 1.0 M px 1.72 / 1.39; C2 2.1 M px 0.563 / 0.592, 0.26 M px 0.305 / 0.268).  Scenes that spill out of the L2 have
+  // the higher floor per level, hence the higher threshold.  RTP_DEEP=paths|wavefront forces one of them.
+  const bool use_paths = s->deep_mode == 1 || (s->deep_mode < 0 && p.n_px <= (s->cfg.scene_exceeds_l2 ? s->paths_px_big : s->paths_px_small));
+  const int wave_levels = use_paths ? std::min(p.max_depth, std::max(1, s->paths_from)) : p.max_depth;
+  for (int d = 0; d < wave_levels; ++d) {
     for (int g = 0; g < G; ++g) { CK(mark(0)); n += launch_closest(gp[g], d, gc[g], gs[g]); CK(stamp("closest", g, d, gs[g])); }
     for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit(gp[g], d, gc[g], gs[g]); CK(stamp("anyhit", g, d, gs[g])); }
     if (p.max_depth > 1)  // max_depth 1: the resolve kernel shades the only level itself
       for (int g = 0; g < G; ++g) { CK(mark(2)); launch_accum(gp[g], d, gs[g]); ++n; CK(stamp("accum", g, d, gs[g])); }
   }
+  if (wave_levels < p.max_depth)
+    for (int g = 0; g < G; ++g) { CK(mark(3)); launch_paths(gp[g], wave_levels, gc[g], gs[g]); ++n; CK(stamp("paths", g, wave_levels, gs[g])); }
   for (int g = 0; g < G; ++g) {
     CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
     CK(stamp("resolve", g, 0, gs[g]));
@@ -823,7 +847,7 @@ int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, s->kev[i], s->kev[i + 1]));
     const int kind = s->kev_kind[(size_t)i];
-    (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : st->ms_shade) += ms;
+    (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : kind == 3 ? st->ms_paths : st->ms_shade) += ms;
   }
   stats_from_counters(s, hg, G, s->last_primary, s->last_depth, s->last_lights, st);
   return RTP_OK;
@@ -1187,6 +1211,7 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
       st->ms_closest = std::max(st->ms_closest, ps.ms_closest);
       st->ms_anyhit = std::max(st->ms_anyhit, ps.ms_anyhit);
       st->ms_shade = std::max(st->ms_shade, ps.ms_shade);
+      st->ms_paths = std::max(st->ms_paths, ps.ms_paths);
       st->kernel_launches += p->last_launches;
     }
     CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // one GPU: includes the overlapped band copies

@@ -39,6 +39,15 @@ constexpr int kMaxDepth = 8;   // direct-colour slots per pixel
 constexpr int kTileDim = 32;   // screen tile edge (multi-GPU interleave unit)
 constexpr int kTilePixels = kTileDim * kTileDim;
 
+// Traversal stack access.  Default: a per-thread array in local memory (L1-resident).  -DRTP_SMEM_STACK=<entries>
+// (experiment build, profiles/r02_design_items.md): the stack lives in shared memory, interleaved over the 128 threads
+// of the CTA (entry i of thread t at [i * 128 + t]: conflict-free when a warp's lanes sit at the same depth).
+#if defined(RTP_SMEM_STACK) && defined(__CUDA_ARCH__)
+#define RTP_STK(s, i) (s)[(i) * 128]
+#else
+#define RTP_STK(s, i) (s)[(i)]
+#endif
+
 struct DeviceScene {
   const float4 *nodes;
   const float4 *tris;
@@ -180,6 +189,7 @@ struct Trav {
   unsigned rbest;
   int sbest;
   bool careful;  // closest-hit re-run: filter every candidate by the reference's box test
+  bool any;      // trav_step<2> only (k_paths: lanes of one warp mix closest-hit and shadow rays): this ray is a shadow ray
 };
 
 RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
@@ -192,11 +202,12 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
   t.o = o; t.d = d;
   t.node = 0;  // the root is always an inner node
   t.sp = 0;
-  stack[0] = kSentinel;
+  RTP_STK(stack, 0) = kSentinel;
   t.tbest = INFINITY;
   t.rbest = 0xffffffffu;
   t.sbest = -1;
   t.careful = false;
+  t.any = false;
 }
 
 // One macro step: descend through inner nodes to the next leaf, then test that leaf (and any
@@ -214,8 +225,11 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
 // box_origin: callable returning the origin for the reference box test.  It is evaluated only when a candidate
 // face has to be filtered (for a frame's shadow rays it is a division and a global load that a step otherwise
 // paid on entry, every time).
-template <bool ANY, class BoxOrigin>
+// MODE 0: closest hit, 1: any hit (compile-time), 2: per ray at run time (t.any) - the deep-path kernel, whose warps hold
+// closest-hit and shadow rays side by side; same arithmetic and the same decisions per ray in every mode.
+template <int MODE, class BoxOrigin>
 RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_origin) {
+  const bool ANY = MODE == 2 ? t.any : MODE == 1;
   int node = t.node, sp = t.sp;
   for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
@@ -234,12 +248,18 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
     bool h0 = c0min <= c0max, h1 = c1min <= c1max;
     int ch0 = f2i(n3.x), ch1 = f2i(n3.y);
     if (!h0 && !h1) {
-      node = stack[sp--];  // stack[0] is the sentinel: popping it ends the ray, sp is not used after
+      node = RTP_STK(stack, sp); --sp;  // stack[0] is the sentinel: popping it ends the ray, sp is not used after
     } else {
       node = h0 ? ch0 : ch1;
       if (h0 && h1) {
         if (!ANY && c1min < c0min) { int tmp = node; node = ch1; ch1 = tmp; }
-        stack[++sp] = ch1;
+        ++sp; RTP_STK(stack, sp) = ch1;
+#if defined(RTP_PREFETCH) && defined(__CUDA_ARCH__)  // experiment build: pull the postponed child towards the L2 now
+        {
+          const void *a = ch1 >= 0 ? (const void *)(S.nodes + 4 * (size_t)ch1) : (const void *)(S.tris + 4 * (size_t)((~ch1) >> 3));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a));
+        }
+#endif
       }
     }
   }
@@ -262,7 +282,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
       t.sbest = first + k;
       if (ANY) { t.node = kSentinel; t.sp = 0; return true; }
     }
-    node = stack[sp--];
+    node = RTP_STK(stack, sp); --sp;
   }
   t.node = node;
   t.sp = sp;
@@ -289,7 +309,7 @@ RTP_HD bool traverse(const DeviceScene &S, v3 o, v3 d, v3 bo, float &best_t, int
   Trav t;
   trav_init(t, o, d, stack);
   do {
-    while (!trav_step<ANY>(S, t, stack, [&] { return bo; })) {}
+    while (!trav_step<ANY ? 1 : 0>(S, t, stack, [&] { return bo; })) {}
   } while (!ANY && closest_needs_rerun(S, t, stack));
   best_t = t.tbest;
   best_slot = t.sbest;

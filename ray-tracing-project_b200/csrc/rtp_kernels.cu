@@ -348,7 +348,12 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
   unsigned long long tm_fetch = tm_start;
   unsigned tm_nb = 0, tm_nc = 0;
 #endif
+#ifdef RTP_SMEM_STACK
+  __shared__ int s_stack[RTP_SMEM_STACK * 128];
+  int *const stack = s_stack + threadIdx.x;
+#else
   int stack[kStackSize];
+#endif
   Trav t;
   int q = 0, age = 0;  // age: steps since this warp last took rays (warp-uniform)
   bool have = false, exhausted = false;
@@ -417,7 +422,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
           e[2] = (int)t.rbest;
           e[3] = t.sbest;
           int n = 0;
-          for (int i = 1; i <= t.sp; ++i) e[5 + n++] = stack[i];
+          for (int i = 1; i <= t.sp; ++i) e[5 + n++] = RTP_STK(stack, i);
           if (t.node != kSentinel) e[5 + n++] = t.node;
           e[4] = n;
           have = false;
@@ -429,7 +434,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
       age = 0;
       continue;
     }
-    if (have && t.node != kSentinel) trav_step<Job::kAny>(job.S, t, stack, [&] { return job.box_origin(q, t); });
+    if (have && t.node != kSentinel) trav_step<Job::kAny ? 1 : 0>(job.S, t, stack, [&] { return job.box_origin(q, t); });
   }
 #ifdef RTP_TRACE_TIMING
   if (lane == 0) {
@@ -560,6 +565,151 @@ __global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int de
       p.ray_d[(depth + 1) & 1][dst] = make_float4(r.x, r.y, r.z, 1.f);
     }
   }
+}
+
+// ---- bounce levels >= 1 in ONE persistent kernel ---------------------------------------------------------------------
+// The wavefront above pays per level: three dependent launches, each as long as its longest ray however few rays the
+// level holds (C4, 10 M triangles: levels 1-5 hold a third of the rays and took two thirds of the frame; on a 1/8 share of
+// the frame every level cost 0.24 ms of pure latency).  Below level 0 the rays are incoherent anyway - there is no
+// screen-space order left to protect - so k_paths drops the level structure: a lane takes a PATH (a reflection ray that
+// k_accum spawned at level 0) and carries it to its end - closest hit (calculateMinimumFace), hit point and
+// interpolated normal, one shadow ray per light (shadow), Phong (calcSingleColor), the reflection ray
+// (flyscene.cpp:317-371), level after level.  A warp's lanes mix closest-hit and shadow rays (trav_step<2>: the kind is a
+// per-ray flag); the state a path carries between traversals lives in shared memory so that the node loop keeps its
+// registers; lanes that have finished a traversal wait until a few of them can go through the (divergent, heavy)
+// shading code together; idle lanes refill from the level-1 ray list.  Same functions, same arithmetic, same results
+// as the wavefront kernels (RTP_DEEP=wavefront selects those; the parity suite runs under both).
+enum { PS_OX, PS_OY, PS_OZ, PS_DX, PS_DY, PS_DZ, PS_PX, PS_PY, PS_PZ, PS_NX, PS_NY, PS_NZ, PS_SX, PS_SY, PS_SZ, PS_FLOATS };
+enum { PS_PIXEL, PS_DEPTH, PS_LIGHT, PS_SLOT, PS_INTS };
+int g_path_wait = 6;  // lanes that must be waiting for the shading block ... (RTP_PATH_WAIT)
+int g_path_run = 12;  // ... unless fewer than this many lanes still traverse (RTP_PATH_RUN)
+
+template <int kRefillBelow>
+__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_paths(const FrameParams p, const int first_depth, const int kPathWait,
+                                                               const int kPathRun) {
+  __shared__ float s_f[PS_FLOATS][128];
+  __shared__ int s_i[PS_INTS][128];
+  __shared__ int s_cnt[2 * kMaxDepth];  // [d] hits at depth d, [kMaxDepth + d] rays spawned into depth d
+  const int tid = threadIdx.x, lane = tid & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  if (tid < 2 * kMaxDepth) s_cnt[tid] = 0;
+  __syncthreads();
+#define PF(k) s_f[k][tid]
+#define PI(k) s_i[k][tid]
+  const DeviceScene &S = p.S;
+  const int n_lights = S.n_lights;
+  const int count = p.counters[kCtrPaths + first_depth];
+  int *const cursor = p.counters + kCtrFetchClosest + first_depth;
+  const float4 *ro = p.ray_o[first_depth & 1], *rd = p.ray_d[first_depth & 1];
+  int stack[kStackSize];
+  Trav t;
+  t.node = kSentinel;
+  t.any = false;
+  bool have = false, exhausted = false;
+  for (;;) {
+    unsigned running = __ballot_sync(kFull, have && t.node != kSentinel);
+    const unsigned waiting = __ballot_sync(kFull, have && t.node == kSentinel);
+    if (waiting && (__popc(waiting) >= kPathWait || __popc(running) < kPathRun)) {
+      if (have && t.node == kSentinel) {
+        bool next_light = false;
+        int li = 0;
+        v3 P, sum;
+        if (!t.any) {  // a closest-hit traversal has ended
+          if (closest_needs_rerun(S, t, stack)) {
+            // careful re-run from the root: keeps traversing
+          } else if (t.sbest < 0) {
+            have = false;  // the path leaves the scene: nothing below contributes (flyscene.cpp:327-332)
+          } else {
+            P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
+            const v3 N = interpolate_normal_slot(S, t.sbest, P);
+            PF(PS_PX) = P.x; PF(PS_PY) = P.y; PF(PS_PZ) = P.z;
+            PF(PS_NX) = N.x; PF(PS_NY) = N.y; PF(PS_NZ) = N.z;
+            PI(PS_SLOT) = t.sbest;
+            sum = mk3(0.f, 0.f, 0.f);
+            atomicAdd(&s_cnt[PI(PS_DEPTH)], 1);
+            next_light = true;
+          }
+        } else {  // the shadow ray towards light PS_LIGHT has ended
+          li = PI(PS_LIGHT);
+          P = mk3(PF(PS_PX), PF(PS_PY), PF(PS_PZ));
+          sum = mk3(PF(PS_SX), PF(PS_SY), PF(PS_SZ));
+          if (t.sbest < 0) {  // not shadowed: calcSingleColor (flyscene.cpp:546-565)
+            const unsigned mat = (unsigned)f2i(__ldg(S.tris + 4 * (size_t)PI(PS_SLOT) + 2).w) & kTriMatMask;
+            const float4 m0 = __ldg(S.materials + 3 * mat), m1 = __ldg(S.materials + 3 * mat + 1), m2 = __ldg(S.materials + 3 * mat + 2);
+            const float4 l1 = __ldg(S.lights + 2 * li + 1);
+            sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, mk3(PF(PS_NX), PF(PS_NY), PF(PS_NZ)), t.d, xyz(l1),
+                                  mk3(PF(PS_OX), PF(PS_OY), PF(PS_OZ)), P));
+          }
+          ++li;
+          next_light = true;
+        }
+        if (next_light) {
+          if (li < n_lights) {  // shadow(P, L) for the next light (flyscene.cpp:510-526,606-612)
+            const float4 l0 = __ldg(S.lights + 2 * li);
+            v3 L = xyz(l0);
+            if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // flyscene.cpp:607
+            PI(PS_LIGHT) = li;
+            PF(PS_SX) = sum.x; PF(PS_SY) = sum.y; PF(PS_SZ) = sum.z;
+            trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);  // flyscene.cpp:512
+            t.any = true;
+          } else {  // the level is done: its clamped direct colour, ks of the (so far) deepest hit, the reflection ray
+            const int depth = PI(PS_DEPTH), pixel = PI(PS_PIXEL);
+            const unsigned mat = (unsigned)f2i(__ldg(S.tris + 4 * (size_t)PI(PS_SLOT) + 2).w) & kTriMatMask;
+            const float4 m2 = __ldg(S.materials + 3 * mat + 2);
+            p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
+            p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
+            if (depth + 1 < p.max_depth) {
+              const v3 r = reflect_dir(mk3(PF(PS_DX), PF(PS_DY), PF(PS_DZ)), mk3(PF(PS_NX), PF(PS_NY), PF(PS_NZ)));  // :361
+              const v3 o2 = vadd(P, vmuls(r, (float)0.001));                                                          // :362
+              PF(PS_OX) = o2.x; PF(PS_OY) = o2.y; PF(PS_OZ) = o2.z;
+              PF(PS_DX) = r.x; PF(PS_DY) = r.y; PF(PS_DZ) = r.z;
+              PI(PS_DEPTH) = depth + 1;
+              atomicAdd(&s_cnt[kMaxDepth + depth + 1], 1);
+              trav_init(t, o2, r, stack);
+            } else {
+              have = false;
+            }
+          }
+        }
+      }
+      running = __ballot_sync(kFull, have && t.node != kSentinel);
+    }
+    const unsigned act = __ballot_sync(kFull, have);
+    if (!exhausted && __popc(act) < kRefillBelow) {
+      const unsigned need = ~act;
+      const int n_need = __popc(need);
+      const int leader = __ffs(need) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(cursor, n_need);
+      base = __shfl_sync(kFull, base, leader);
+      exhausted = base + n_need >= count;
+      if (!have) {
+        const int q = base + __popc(need & lt);
+        if (q < count) {
+          const float4 o4 = ro[q], d4 = rd[q];
+          PF(PS_OX) = o4.x; PF(PS_OY) = o4.y; PF(PS_OZ) = o4.z;
+          PF(PS_DX) = d4.x; PF(PS_DY) = d4.y; PF(PS_DZ) = d4.z;
+          PI(PS_PIXEL) = f2i(o4.w);
+          PI(PS_DEPTH) = first_depth;
+          trav_init(t, xyz(o4), xyz(d4), stack);
+          have = true;
+        }
+      }
+      running = __ballot_sync(kFull, have && t.node != kSentinel);
+    }
+    if (running == 0) {
+      if (__ballot_sync(kFull, have) == 0 && exhausted) break;
+      continue;
+    }
+    if (have && t.node != kSentinel)
+      // origin of the reference's BoundingBox test: the un-offset hit point for a shadow ray, the ray's own origin
+      // for a (careful) closest-hit ray
+      trav_step<2>(S, t, stack, [&] { return t.any ? mk3(PF(PS_PX), PF(PS_PY), PF(PS_PZ)) : t.o; });
+  }
+#undef PF
+#undef PI
+  __syncthreads();
+  if (tid < 2 * kMaxDepth && s_cnt[tid]) atomicAdd(p.counters + (tid < kMaxDepth ? kCtrHits + tid : kCtrPaths + tid - kMaxDepth), s_cnt[tid]);
 }
 
 // the fold of traceRay's return values (flyscene.cpp:366-370 with the member ks of the deepest hit)
@@ -795,6 +945,9 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny<true>, 1>, cfg.threads, 0);
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
+  int b2 = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_paths<24>, 128, 0);
+  cfg.blocks_paths = sms * (b2 > 0 ? b2 : 1);
   cfg.blocks_coop = sms * 2;
   if (const char *e = std::getenv("RTP_COOP_BLOCKS")) cfg.blocks_coop = sms * std::max(1, std::atoi(e));  // per SM (tuning runs)
 }
@@ -850,6 +1003,19 @@ static int launch_anyhit_t(const FrameParams &p, int depth, const LaunchCfg &cfg
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
   if (depth == 0 && !p.user_rays) return launch_anyhit_t<true>(p, depth, cfg, st);  // camera level: dense records
   return launch_anyhit_t<false>(p, depth, cfg, st);
+}
+
+void launch_paths(const FrameParams &p, int first_depth, const LaunchCfg &cfg, cudaStream_t st) {
+  static int refill = -1;
+  if (refill < 0) {
+    const char *e = std::getenv("RTP_PATH_REFILL");
+    refill = e ? std::atoi(e) : 24;
+    if ((e = std::getenv("RTP_PATH_WAIT"))) g_path_wait = std::atoi(e);
+    if ((e = std::getenv("RTP_PATH_RUN"))) g_path_run = std::atoi(e);
+  }
+  if (refill <= 8) k_paths<8><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
+  else if (refill <= 24) k_paths<24><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
+  else k_paths<32><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
 }
 
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st) {

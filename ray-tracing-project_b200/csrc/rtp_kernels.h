@@ -46,7 +46,7 @@ struct FrameParams {
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, threads = 128;
   int *park_slots = nullptr;  // parked-ray list storage (park_cap * kParkSlotBytes), owned by the scene
   int park_cap = 0;
   bool scene_exceeds_l2 = false;  // nodes + triangles larger than half the L2: traversal chains run on cold lines
@@ -61,6 +61,9 @@ void launch_raygen(const FrameParams &p, cudaStream_t st);
 int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
 // shadow() for every (hit, light) pair (flyscene.cpp:510-526)
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// every bounce level from first_depth on, path by path, in one persistent kernel (k_paths): replaces the per-level
+// launch_closest / launch_anyhit / launch_accum sequence below the camera level
+void launch_paths(const FrameParams &p, int first_depth, const LaunchCfg &cfg, cudaStream_t st);
 // calcSingleColor / calculateColor + reflection-ray spawn (flyscene.cpp:542-566,603-614,355-363); not needed when
 // max_depth is 1 (launch_resolve shades the single level itself)
 void launch_accum(const FrameParams &p, int depth, cudaStream_t st);

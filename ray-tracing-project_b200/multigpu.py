@@ -74,6 +74,8 @@ class PeerImage:
         self.frame = 0
         self.token = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", device_index))
         self.counter = self.base + 2 * self.stride  # uint32 in rank 0's memory, reached by every rank over NVLink
+        self.start_counter = self.counter + 64      # a second counter: align_start
+        self.starts = 0
         if world > 1:
             dist.barrier()  # every rank has the block mapped before anybody's first frame arrives at the counter
 
@@ -95,6 +97,17 @@ class PeerImage:
         if getattr(self, "base", None):
             self.rtp.shared_free(self.dev, self.base, self.opened)
             self.base = None
+
+
+def align_start(scene, img, stream, timeout_ms=10000):
+    """Device-side start line: enqueued on `stream` in front of a frame, every rank's GPU waits (rtp_peer_barrier on a
+    second counter of the shared block) until all ranks' GPUs have reached it - what is enqueued behind it starts within
+    a microsecond or two on all GPUs, whatever the skew between the ranks' host threads; the hosts are not blocked and
+    keep enqueueing the frame meanwhile.  Measurement plumbing (bench.py places it before the start event of a timed
+    step, after the host barrier): the timed region then begins at the same instant on every GPU."""
+    if img.world > 1:
+        img.starts += 1
+        scene.peer_barrier(img.start_counter, img.world * img.starts, timeout_ms, stream)
 
 
 def render_frame_peer(scene, img, max_depth, stream, flags=0, barrier="peer", timeout_ms=10000):

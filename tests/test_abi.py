@@ -31,7 +31,7 @@ def test_struct_sizes_match_header(rtp):
     assert C.sizeof(rtp.RtpMesh) == 16 + 6 * 8 + 48 + 3 * 8 + 16
     assert C.sizeof(rtp.RtpCamera) == 48 + 16 + 8
     assert C.sizeof(rtp.RtpRenderOpts) == 12 + 12 + 12
-    assert C.sizeof(rtp.RtpStats) == 32 + 8 + 12 + 12
+    assert C.sizeof(rtp.RtpStats) == 32 + 8 + 12 + 12 + 8
 
 
 def test_invalid_arguments_are_rejected(rtp):

@@ -270,3 +270,27 @@ def test_far_camera_matches_the_oracle(rtp, po, seed, dist):
         assert (o["hit"] >= 0).mean() > 0.05
         check_image(out["rgb"].reshape(-1, 3), out["hit"].ravel(), o["rgb"], o["hit"], exact_fraction=0.5)
     s.close()
+
+
+@pytest.mark.parametrize("name", ["dodge_c2", "cube_rot", "plane_diag", "quirks", "soft17_dodge"])
+def test_path_kernel_equals_the_per_level_kernels(rtp, name, monkeypatch):
+    """Bounce levels >= 1 run either path by path in one persistent kernel (k_paths: RTP_DEEP=paths, the default for
+    small frames) or as per-level closest / shadow / shade launches (RTP_DEEP=wavefront, the default for big frames);
+    the variable is read when the scene is created.  Same functions, same arithmetic:
+    the two frames must agree bit for bit, ray counters included."""
+    c = load_case(name)
+    m = load_golden_mesh(c["model"])
+    w, h = 3 * int(c["w"]), 3 * int(c["h"])
+    frames = []
+    for mode in ("paths", "wavefront"):
+        monkeypatch.setenv("RTP_DEEP", mode)
+        s = make_scene(rtp, m)
+        s.set_lights(c["point_lights"], c["dir_lights"])
+        s.set_camera(w, h, c["view"])
+        frames.append(s.render(w, h, max_depth=6, want=("rgb", "hit")))
+        s.close()
+    a, b = frames
+    assert np.array_equal(a["hit"], b["hit"]) and bits_equal(a["rgb"], b["rgb"]).all()
+    for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits"):
+        assert a["stats"][k] == b["stats"][k], k
+    assert a["stats"]["kernel_launches"] < b["stats"]["kernel_launches"]
