@@ -450,6 +450,7 @@ def run_ours(args, wl, rtp):
         roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, n_tris, torch.cuda.get_device_properties(local).multi_processor_count,
                              clocks, peaks,
                              extra=dict(kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
+                                        rays_by_kind=dict(closest=own[0], anyhit=own[1]),
                                         kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events on the launch "
                                                         f"stream, the frame as one tile group (each kernel alone on the GPU, k_coop counted with its "
                                                         f"k_trace), {float(np.mean(ms_serial)):.4f} ms per step"))
