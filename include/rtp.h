@@ -229,6 +229,22 @@ int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max
 int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode, void *d_face,
                           void *d_t, void *d_occluded, void *stream, rtp_stats *st);
 
+/* rtp_trace_rays_device for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same rays, modes (CLOSEST or ANYHIT) and outputs as rtp_trace_rays_device, no statistics.  The call allocates
+ * nothing, on the device or through any library: the scratch the trace kernels need (ray cursor, parked-ray counters
+ * and RTP_NOALLOC_PARK_SLOTS parked-ray slots, 1 180 160 bytes) is a static __device__ array of the library that every
+ * GPU loading it holds until exit.  Limits: n <= RTP_NOALLOC_MAX_RAYS per call (RTP_ERR_INVALID beyond, split the
+ * batch).  Every call on a device shares that one array - also calls on different scenes: calls that overlap on the GPU
+ * (different streams, no ordering between them) race and give undefined hits; calls on one stream, or ordered by
+ * events, are fine.  The array keeps the last call's contents; the call clears what must start at zero itself
+ * (cudaMemsetAsync on `stream`).  It does not wait for or order itself against the scene's frames (it reads the scene
+ * arrays only), and - as rtp_trace_rays_device - it does not widen the hierarchy for far-away ray origins. */
+#define RTP_NOALLOC_MAX_RAYS (1 << 22)
+#define RTP_NOALLOC_PARK_SLOTS 4096
+int rtp_trace_rays_device_noalloc(rtp_scene *s, const void *d_rays, int64_t n, int mode, void *d_face, void *d_t,
+                                  void *d_occluded, void *stream);
+
 /* ---- introspection ------------------------------------------------------------------------ */
 /* BoundingBox::boxes view of the scene (BoundingBox.h:13): sizes, then copies. */
 int rtp_scene_box_count(const rtp_scene *s);

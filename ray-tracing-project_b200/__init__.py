@@ -64,7 +64,7 @@ EXPORTS = ["rtp_scene_create", "rtp_scene_destroy", "rtp_set_lights", "rtp_set_c
            "rtp_trace_rays_device", "rtp_scene_box_count", "rtp_scene_get_boxes", "rtp_scene_info",
            "rtp_last_error", "rtp_abi_version", "rtp_set_tile_groups", "rtp_get_tile_groups", "rtp_render_async", "rtp_render_wait", "rtp_peer_barrier", "rtp_peer_barrier_timeouts", "rtp_frame_stats", "rtp_tile_table", "rtp_render_image_device",
            "rtp_shared_alloc", "rtp_shared_open", "rtp_shared_free", "rtp_scene_create_multi", "rtp_scene_device_count",
-           "rtp_device_count", "rtp_peer_barrier_reset"]
+           "rtp_device_count", "rtp_peer_barrier_reset", "rtp_trace_rays_device_noalloc"]
 
 _lib = None
 
@@ -108,6 +108,8 @@ def lib():
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(RtpStats)]
         L.rtp_trace_rays_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p, C.POINTER(RtpStats)]
+        L.rtp_trace_rays_device_noalloc.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p]
         L.rtp_scene_box_count.argtypes = [C.c_void_p]
         L.rtp_scene_get_boxes.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.rtp_scene_info.argtypes = [C.c_void_p, C.POINTER(RtpStats)]
@@ -357,6 +359,10 @@ class Scene:
         self._check(self._L.rtp_trace_rays_device(self._h, d_rays_ptr, n, mode, d_face, d_t, d_occ, stream,
                                                   C.byref(st) if want_stats else None))
         return st.as_dict() if want_stats else None
+
+    def trace_rays_device_noalloc(self, d_rays_ptr, n, mode, d_face=None, d_t=None, d_occ=None, stream=None):
+        """rtp_trace_rays_device_noalloc: the same launches with the library's static scratch, nothing allocated."""
+        self._check(self._L.rtp_trace_rays_device_noalloc(self._h, d_rays_ptr, n, mode, d_face, d_t, d_occ, stream))
 
 
 SHARED_HANDLE_BYTES = 64

@@ -1352,6 +1352,26 @@ int rtp_trace_rays_device(rtp_scene *s, const void *d_rays, int64_t n, int mode,
   return RTP_OK;
 }
 
+int rtp_trace_rays_device_noalloc(rtp_scene *s, const void *d_rays, int64_t n, int mode, void *d_face, void *d_t,
+                                  void *d_occluded, void *stream) {
+  if (!s || !d_rays || n < 0) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device_noalloc: bad argument");
+  if (n > (int64_t)RTP_NOALLOC_MAX_RAYS)
+    return fail(RTP_ERR_INVALID, "rtp_trace_rays_device_noalloc: " + std::to_string(n) + " rays exceed the limit of " +
+                                     std::to_string(RTP_NOALLOC_MAX_RAYS) + " per call (split the batch, or use rtp_trace_rays_device)");
+  if (mode != RTP_RAYS_CLOSEST && mode != RTP_RAYS_ANYHIT)
+    return fail(RTP_ERR_INVALID, "rtp_trace_rays_device_noalloc: mode must be CLOSEST or ANYHIT");
+  if (mode == RTP_RAYS_CLOSEST && !d_face) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device_noalloc: face output required");
+  if (mode == RTP_RAYS_ANYHIT && !d_occluded) return fail(RTP_ERR_INVALID, "rtp_trace_rays_device_noalloc: occluded output required");
+  if (n == 0) return RTP_OK;
+  DeviceGuard g(s->device);
+  // nothing of the scene's mutable state is touched (no counters, no parked-ray list, no events): the launch reads the
+  // scene arrays and works in the library's static scratch, which it shares with every other call on this device
+  int launches = 0;
+  CK(launch_rays_noalloc(s->device, s->dS, (const float *)d_rays, n, mode == RTP_RAYS_ANYHIT, (int *)d_face, (float *)d_t,
+                         (unsigned char *)d_occluded, s->cfg, (cudaStream_t)stream, &launches));
+  return RTP_OK;
+}
+
 int rtp_trace_rays(rtp_scene *s, const float *rays, int64_t n, int mode, int max_depth, const float background[3],
                    float *rgb, int32_t *face, float *t, uint8_t *occluded, rtp_stats *st) {
   if (!s || !rays || n <= 0 || n > (int64_t)0x7f000000) return fail(RTP_ERR_INVALID, "rtp_trace_rays: bad argument");

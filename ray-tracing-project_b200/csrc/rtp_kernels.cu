@@ -22,6 +22,7 @@
 #include "rtp_kernels.h"
 
 #include <cstdlib>
+#include <mutex>
 
 namespace rtp {
 
@@ -1054,6 +1055,45 @@ int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, uns
   RaysAny j;
   j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
   return launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, 1ll << 40, st);  // ray batches: never (C5)
+}
+
+// ---- ray batches without any allocation (rtp_trace_rays_device_noalloc) ----------------------------------------
+// The scratch a ray-batch launch needs - the ray cursor, the parked-ray counters and the parked-ray slots that the
+// scene otherwise owns (cudaMalloc at rtp_scene_create) - lives in this file-scope array instead: every GPU that loads
+// the library holds kNoAllocBytes until exit.  Head = one counters block (same layout as a frame's, so launch_trace is
+// shared), then kNoAllocParkCap parked-ray slots.  In host code `g_noalloc_scratch` is only a stand-in for the symbol:
+// the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+constexpr int kNoAllocHeadInts = 128;  // >= kCtrInts, keeps the slots 256-byte aligned
+static_assert(kNoAllocHeadInts >= kCtrInts, "counters block must fit the head of the no-alloc scratch");
+constexpr size_t kNoAllocInts = kNoAllocHeadInts + (size_t)kNoAllocParkCap * (kParkSlotBytes / sizeof(int));
+static __device__ __align__(256) int g_noalloc_scratch[kNoAllocInts];
+
+cudaError_t launch_rays_noalloc(int device, const DeviceScene &S, const float *rays, long long n, int any, int *face,
+                                float *t, unsigned char *occ, LaunchCfg cfg, cudaStream_t st, int *launches) {
+  constexpr int kMaxDev = 64;
+  static int *ptr_of[kMaxDev];  // per device: the array's address there (0 = not asked yet)
+  static std::mutex mu;
+  if (device < 0 || device >= kMaxDev) return cudaErrorInvalidDevice;
+  int *scratch;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr_of[device]) {  // the caller made `device` current (DeviceGuard)
+      int *p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+      if (e != cudaSuccess) return e;
+      ptr_of[device] = p;
+    }
+    scratch = ptr_of[device];
+  }
+  // what must start at zero: the ray cursor and the launch's (rays parked, k_coop cursor) pair; the slots are
+  // written before they are read and keep the previous call's contents
+  cudaError_t e = cudaMemsetAsync(scratch, 0, kNoAllocHeadInts * sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  cfg.park_slots = scratch + kNoAllocHeadInts;
+  cfg.park_cap = kNoAllocParkCap;
+  int *cursor = scratch + kCtrAux;
+  *launches = any ? launch_rays_anyhit(S, rays, n, occ, cursor, cfg, st) : launch_rays_closest(S, rays, n, face, t, cursor, cfg, st);
+  return cudaGetLastError();
 }
 
 }  // namespace rtp

@@ -86,4 +86,11 @@ int launch_rays_closest(const DeviceScene &S, const float *rays, long long n, in
 int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, unsigned char *occ, int *cursor,
                         const LaunchCfg &cfg, cudaStream_t st);
 
+// The same two launches with their scratch (ray cursor, parked-ray counters and slots) in a file-scope __device__ array
+// of rtp_kernels.cu instead of the scene's cudaMalloc'ed blocks: nothing is allocated, every call on a device shares the
+// array.  `device` must be current.  any: 0 = closest hit (face, t), 1 = any hit (occ).
+constexpr int kNoAllocParkCap = 4096;  // parked-ray slots in the array (a ray that finds the list full carries on)
+cudaError_t launch_rays_noalloc(int device, const DeviceScene &S, const float *rays, long long n, int any, int *face,
+                                float *t, unsigned char *occ, LaunchCfg cfg, cudaStream_t st, int *launches);
+
 }  // namespace rtp
