@@ -33,8 +33,11 @@ def kind_of(name):
 
 def main():
     workload, rep, bench = sys.argv[1], sys.argv[2], sys.argv[3]
-    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
-    rows = list(csv.reader(out.splitlines()))
+    if rep.endswith(".csv"):  # `ncu -i capture.ncu-rep --page raw --csv` written on the GPU box (a .ncu-rep of 50 launches is too big to bring back)
+        out = open(rep).read()
+    else:
+        out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], stdout=subprocess.PIPE, text=True).stdout
+    rows = [r for r in csv.reader(out.splitlines()) if r and not r[0].startswith("==")]
     H, U, data = rows[0], rows[1], rows[2:]
     ki = H.index("Kernel Name")
 

@@ -186,6 +186,10 @@ struct rtp_scene {
   int *counters_pinned = nullptr;           // page-locked landing place of a frame's counters (rtp_render)
   unsigned async_head = 0, async_tail = 0;  // frames enqueued / waited for
   bool in_async_call = false;
+  // RTP_L2_PERSIST=<MiB> (experiment, profiles/r02_design_items.md): that much of the L2 is set aside for persisting
+  // lines and every stream a frame runs on gets an access-policy window over the head of the node array
+  int l2_persist_mb = 0;
+  std::vector<cudaStream_t> l2_streams;  // streams that carry the window already
   int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
   int last_groups = 1;  // groups of the most recently enqueued frame (their counters are summed)
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
@@ -249,6 +253,30 @@ int init_device_side(rtp_scene *s) {
   if (const char *te = std::getenv("RTP_PATHS_PX_SMALL")) s->paths_px_small = std::atoi(te);
   if (const char *pe = std::getenv("RTP_PATHS_FROM")) s->paths_from = std::atoi(pe);
   if (const char *ge = std::getenv("RTP_GROUPS")) s->groups = std::min(std::max(std::atoi(ge), 0), kMaxGroups);
+  if (const char *le = std::getenv("RTP_L2_PERSIST")) {
+    s->l2_persist_mb = std::max(std::atoi(le), 0);
+    if (s->l2_persist_mb) CK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)s->l2_persist_mb << 20));
+  }
+  return RTP_OK;
+}
+
+// RTP_L2_PERSIST: kernels launched into `st` keep the lines of the node array's head in the persisting part of the L2
+int apply_l2_window(rtp_scene *s, cudaStream_t st) {
+  if (s->l2_persist_mb <= 0 || std::find(s->l2_streams.begin(), s->l2_streams.end(), st) != s->l2_streams.end()) return RTP_OK;
+  int max_window = 0;
+  CK(cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, s->device));
+  const size_t want = (size_t)s->host.n_nodes * 64, carve = (size_t)s->l2_persist_mb << 20;
+  const size_t bytes = std::min(want, (size_t)std::max(max_window, 0));
+  if (!bytes) return RTP_OK;
+  cudaStreamAttrValue v;
+  std::memset(&v, 0, sizeof v);
+  v.accessPolicyWindow.base_ptr = (void *)s->nodes.p;
+  v.accessPolicyWindow.num_bytes = bytes;
+  v.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)carve / (double)bytes);
+  v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+  v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+  CK(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v));
+  s->l2_streams.push_back(st);
   return RTP_OK;
 }
 
@@ -754,6 +782,7 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     gc[g].park_cap = s->cfg.park_cap / G;
     gc[g].park_slots = s->cfg.park_slots + (size_t)g * gc[g].park_cap * (kParkSlotBytes / sizeof(int));
     gs[g] = g == 0 ? st : s->gstream[g];
+    if (s->l2_persist_mb) { int lrc = apply_l2_window(s, gs[g]); if (lrc) return lrc; }
   }
   const bool fork = G > 1 && !profile;
   if (fork) {

@@ -88,6 +88,27 @@ RTP_HD v3 xyz(float4 a) { return mk3(a.x, a.y, a.z); }
 #endif
 RTP_HD v3 pinned(v3 a) { RTP_PIN(a.x); RTP_PIN(a.y); RTP_PIN(a.z); return a; }
 
+// -DRTP_CHECKED (variant build libflyscene_b200_checked.so, profiles/r02_checked.md): bounds checks of the library's own
+// on every index the kernels form - traversal stack, node / triangle / BoundingBox ids, parked-ray slots, k_coop's
+// shared stack, hit records, ray lists, image pixels.  (compute-sanitizer is closed on the pool this is developed on.)
+// A failed check is counted, its first code and value kept; rtp_debug_checks() reads the block.  Off in the product.
+#if defined(RTP_CHECKED) && defined(__CUDACC__)
+static __device__ unsigned g_rtp_check[4];  // [0] failed checks, [1] code of the first, [2] its value, [3] its limit
+#define RTP_CHECK(cond, code, val, lim)                                                                       \
+  do {                                                                                                        \
+    if (!(cond)) {                                                                                            \
+      if (atomicAdd(&g_rtp_check[0], 1u) == 0u) { g_rtp_check[1] = (code); g_rtp_check[2] = (unsigned)(val); g_rtp_check[3] = (unsigned)(lim); } \
+    }                                                                                                         \
+  } while (0)
+#else
+#define RTP_CHECK(cond, code, val, lim) ((void)0)
+#endif
+#if defined(RTP_CHECKED) && defined(__CUDA_ARCH__)
+#define RTP_CHECK_DEV(cond, code, val, lim) RTP_CHECK(cond, code, val, lim)
+#else
+#define RTP_CHECK_DEV(cond, code, val, lim) ((void)0)
+#endif
+
 // Traversal work counters: compiled in only for tests/hostsim (CPU, -DRTP_TRAV_STATS), where they
 // give nodes / leaves / triangle tests per ray for the roofline discussion in DESIGN.md.
 #if defined(RTP_TRAV_STATS) && !defined(__CUDA_ARCH__)
@@ -233,6 +254,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
   int node = t.node, sp = t.sp;
   for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
+    RTP_CHECK_DEV(node < S.n_nodes, 1, node, S.n_nodes);
     RTP_STAT(nodes);
     float4 n0 = RTP_LDG4(Np), n1 = RTP_LDG4(Np + 1), n2 = RTP_LDG4(Np + 2), n3 = RTP_LDG4(Np + 3);
     float c0lox = fmaf(n0.x, t.idx, -t.oodx), c0hix = fmaf(n0.y, t.idx, -t.oodx);
@@ -254,6 +276,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
       if (h0 && h1) {
         if (!ANY && c1min < c0min) { int tmp = node; node = ch1; ch1 = tmp; }
         ++sp; RTP_STK(stack, sp) = ch1;
+        RTP_CHECK_DEV(sp < kStackSize, 2, sp, kStackSize);
 #if defined(RTP_PREFETCH) && defined(__CUDA_ARCH__)  // experiment build: pull the postponed child towards the L2 now
         {
           const void *a = ch1 >= 0 ? (const void *)(S.nodes + 4 * (size_t)ch1) : (const void *)(S.tris + 4 * (size_t)((~ch1) >> 3));
@@ -266,6 +289,7 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
   while (node < 0) {
     int enc = ~node;
     int first = enc >> 3, cnt = (enc & 7) + 1;
+    RTP_CHECK_DEV(first + cnt <= S.n_tris, 3, first + cnt, S.n_tris);
     RTP_STAT(leaves);
     for (int k = 0; k < cnt; ++k) {
       RTP_STAT(tris);
@@ -276,12 +300,14 @@ RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_o
       // tt <= tbest here.  Equal t: the first-visited face wins (flyscene.cpp:387 is a strict <),
       // and t == +inf never beats the initial INFINITY.
       if (!ANY && !(tt < t.tbest || (t.sbest >= 0 && rank < t.rbest))) continue;
+      RTP_CHECK_DEV((unsigned)f2i(T1.w) < (unsigned)S.n_boxes, 4, f2i(T1.w), S.n_boxes);
       if ((ANY || t.careful) && !ref_box_pass(S, pinned(box_origin()), pinned(t.d), f2i(T1.w))) continue;  // invisible to the reference
       t.tbest = ANY ? t.tbest : tt;
       t.rbest = rank;
       t.sbest = first + k;
       if (ANY) { t.node = kSentinel; t.sp = 0; return true; }
     }
+    RTP_CHECK_DEV(sp >= 0, 5, sp, 0);
     node = RTP_STK(stack, sp); --sp;
   }
   t.node = node;

@@ -56,9 +56,10 @@ struct FrameClosest {
   float4 *ksdeep;  // level 0 only: zeroed for pixels without a hit (k_accum / k_shade_image write the others)
   int *cursor;
   const int *count_ptr;  // device counter (depth > 0) or null
-  int count_fixed;
+  int count_fixed;       // = n_px: the capacity of every per-path and per-hit-record buffer above
   __device__ __forceinline__ int count() const { return count_ptr ? *count_ptr : count_fixed; }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    RTP_CHECK((unsigned)q < (unsigned)count_fixed, 10, q, count_fixed);
     if (CAM) {
       const int tile = __ldg(tile_ids + (q >> 10));
       int x, y;
@@ -101,6 +102,8 @@ struct FrameClosest {
       }
     }
     if (hit) {
+      RTP_CHECK((unsigned)h < (unsigned)count_fixed, 11, h, count_fixed);
+      RTP_CHECK((unsigned)t.sbest < (unsigned)S.n_tris, 12, t.sbest, S.n_tris);
       const v3 P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
       pbuf[h] = make_float4(P.x, P.y, P.z, i2f(t.sbest));
       dbuf[h] = make_float4(t.d.x, t.d.y, t.d.z, i2f(CAM ? q : f2i(ro[q].w)));
@@ -143,6 +146,7 @@ struct FrameAny {
   }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
     const int h = q / S.n_lights;
+    RTP_CHECK((unsigned)h < (unsigned)n_px, 13, h, n_px);
     if (DENSE && hit_slot[h] < 0) return false;
     const v3 P = xyz(pbuf[h]);
     const v3 L = light_dir(q, P);
@@ -165,6 +169,7 @@ struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
   int n;
   __device__ __forceinline__ int count() const { return n; }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    RTP_CHECK((unsigned)q < (unsigned)n, 14, q, n);
     const float *r = rays + 6 * (size_t)q;
     trav_init(t, mk3(r[0], r[1], r[2]), mk3(r[3], r[4], r[5]), stack);
     return true;
@@ -188,6 +193,7 @@ struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
   int n;
   __device__ __forceinline__ int count() const { return n; }
   __device__ __forceinline__ bool init(int q, Trav &t, int *stack) const {
+    RTP_CHECK((unsigned)q < (unsigned)n, 15, q, n);
     const float *r = rays + 6 * (size_t)q;
     const v3 P = mk3(r[0], r[1], r[2]), L = mk3(r[3], r[4], r[5]);
     trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
@@ -255,6 +261,7 @@ __device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const 
     if (lane < k) {
       if (my >= 0) {
         const float4 *Np = S.nodes + 4 * (size_t)my;
+        RTP_CHECK(my < S.n_nodes, 21, my, S.n_nodes);
         const float4 n0 = __ldg(Np), n1 = __ldg(Np + 1), n2 = __ldg(Np + 2), n3 = __ldg(Np + 3);
         const float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
         const float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
@@ -278,6 +285,7 @@ __device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const 
       } else {
         const int enc = ~my;
         const int first = enc >> 3, cnt = (enc & 7) + 1;
+        RTP_CHECK(first + cnt <= S.n_tris, 22, first + cnt, S.n_tris);
         for (int j = 0; j < cnt; ++j) {
           float tt;
           float4 T0, T1;
@@ -311,6 +319,7 @@ __device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const 
     const bool pf = push_far != kSentinel, pn = push_near != kSentinel;
     const unsigned bf = __ballot_sync(kFull, pf), bn = __ballot_sync(kFull, pn);
     const int pos = n + __popc(bf & gt) + __popc(bn & gt);  // entries of higher lanes go below
+    RTP_CHECK(pos + 1 < kCoopStack, 20, pos + 1, kCoopStack);
     if (pf) ws[pos] = push_far;
     if (pn) ws[pos + (pf ? 1 : 0)] = push_near;
     n += __popc(bf) + __popc(bn);
@@ -425,6 +434,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
           int n = 0;
           for (int i = 1; i <= t.sp; ++i) e[5 + n++] = RTP_STK(stack, i);
           if (t.node != kSentinel) e[5 + n++] = t.node;
+          RTP_CHECK(5 + n <= kParkInts, 23, 5 + n, kParkInts);
           e[4] = n;
           have = false;
 #ifdef RTP_TRACE_TIMING
@@ -472,6 +482,7 @@ __global__ void __launch_bounds__(128, 4) k_coop(const Job job, const ParkList p
     job.init(q, t, stack);  // the same ray in every lane
     t.tbest = i2f(e[1]); t.rbest = (unsigned)e[2]; t.sbest = e[3]; t.careful = ex < 0;
     int n = e[4];
+    RTP_CHECK(n >= 0 && 5 + n <= kParkInts && (unsigned)q < 0x7f000000u, 24, n, kParkInts - 5);
     for (int i = lane; i < n; i += 32) ws[i] = e[5 + i];
     __syncwarp();
     for (;;) {
@@ -548,6 +559,7 @@ __global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int de
     float4 ks;
     v3 normal;
     const v3 c = shade_hit(p, h, o, P, f2i(pb.w), normal, ks);
+    RTP_CHECK((unsigned)pixel < (unsigned)p.n_px && (unsigned)depth < (unsigned)p.max_depth, 33, pixel, p.n_px);
     p.direct[(size_t)depth * p.n_px + pixel] = make_float4(c.x, c.y, c.z, 0.f);
     p.ksdeep[pixel] = make_float4(ks.x, ks.y, ks.z, i2f(depth + 1));
     if (spawn) {
@@ -562,6 +574,7 @@ __global__ void __launch_bounds__(256) k_accum(const FrameParams p, const int de
     if (lane == leader) dst = atomicAdd(p.counters + kCtrPaths + depth + 1, __popc(m));
     dst = __shfl_sync(kFull, dst, leader) + __popc(m & ((1u << lane) - 1u));
     if (spawn) {
+      RTP_CHECK((unsigned)dst < (unsigned)p.n_px && (unsigned)pixel < (unsigned)p.n_px, 30, dst, p.n_px);
       p.ray_o[(depth + 1) & 1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(pixel));
       p.ray_d[(depth + 1) & 1][dst] = make_float4(r.x, r.y, r.z, 1.f);
     }
@@ -657,6 +670,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_paths(const FrameParams
             const int depth = PI(PS_DEPTH), pixel = PI(PS_PIXEL);
             const unsigned mat = (unsigned)f2i(__ldg(S.tris + 4 * (size_t)PI(PS_SLOT) + 2).w) & kTriMatMask;
             const float4 m2 = __ldg(S.materials + 3 * mat + 2);
+            RTP_CHECK((unsigned)pixel < (unsigned)p.n_px && (unsigned)depth < (unsigned)p.max_depth, 31, pixel, p.n_px);
             p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
             p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
             if (depth + 1 < p.max_depth) {
@@ -780,6 +794,7 @@ __global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
   float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
   if (valid) out = SHADE1 ? shade_pixel_depth1(p, q) : resolve_pixel(p, q);
   const size_t idx = (size_t)j * p.width + i;
+  RTP_CHECK(!valid || (idx < (size_t)p.width * p.height && q < p.n_px), 32, idx, p.width * p.height);
   if (valid && p.fb) p.fb[q] = out;
   if (valid && p.img_rgb) {  // float plane, row-major: a warp stores 384 consecutive bytes
     p.img_rgb[3 * idx] = out.x;
@@ -1098,6 +1113,10 @@ cudaError_t launch_rays_noalloc(int device, const DeviceScene &S, const float *r
 
 }  // namespace rtp
 
+#ifdef RTP_CHECKED
+// failed bounds checks since the library was loaded: out[0] count, out[1..3] code / value / limit of the first
+extern "C" int rtp_debug_checks(unsigned *out) { return (int)cudaMemcpyFromSymbol(out, rtp::g_rtp_check, 4 * sizeof(unsigned)); }
+#endif
 #ifdef RTP_TRACE_TIMING
 extern "C" int rtp_debug_timing(unsigned long long *out) {
   return (int)cudaMemcpyFromSymbol(out, rtp::g_warp_timing, sizeof(unsigned long long) * 2 * 8192 * 8);
