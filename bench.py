@@ -173,7 +173,7 @@ class ClockSampler:
                 self.rows.append((time.perf_counter(), float(mhz), int(reasons)))
             except Exception:
                 pass
-            time.sleep(0.004)
+            time.sleep(0.001)
 
     def stop(self, t_begin=None, t_end=None):
         self.stop_flag = True
@@ -194,7 +194,7 @@ class ClockSampler:
             mask |= r[2]
         return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=self.max_mhz,
                     reasons=sorted(k for k, bit in self.BAD.items() if mask & bit), samples=len(sm),
-                    how="NVML, 4 ms period, samples inside the timed region")
+                    how="NVML, 1 ms period, samples inside the timed region")
 
 
 def cpu_baseline_port(wl, n_rays_target=None, seconds=15.0):
@@ -353,7 +353,12 @@ def run_ours(args, wl, rtp):
 
     t_begin = time.perf_counter()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ms_steps, k_closest, k_any, k_shade = [], [], [], []
+    ms_steps, k_closest, k_any, k_shade, k_cam = [], [], [], [], []
+    # rays of the camera level alone (k_camera's launch): one untimed frame at max_depth 1 on this rank's tiles
+    scene.render_tiles_device(w, h, tg.tiles.data_ptr(), max_depth=1, rank=rank, world=world, stream=stream)
+    torch.cuda.synchronize()
+    st1 = scene.frame_stats()
+    rays_camera = float(st1["rays_primary"] + st1["rays_shadow"])
     for _ in range(args.steps):
         flush.zero_()          # evict the scene from L2 between timed iterations (untimed)
         sync_all()
@@ -387,6 +392,7 @@ def run_ours(args, wl, rtp):
         k_closest.append(fs["ms_closest"])
         k_any.append(fs["ms_anyhit"])
         k_shade.append(fs["ms_shade"])
+        k_cam.append(fs["ms_camera"])
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
     e2e_ms = []
@@ -444,16 +450,21 @@ def run_ours(args, wl, rtp):
         peaks = load_peaks()
         n_tris = info["n_triangles"]
         mc, ms_, mo = float(np.mean(k_closest)), float(np.mean(k_any)), float(np.mean(k_shade))
-        own = float(st["rays_primary"] + st["rays_reflection"]), float(st["rays_shadow"])
-        dom = "k_trace<closest>" if mc >= ms_ else "k_trace<anyhit>"
-        dom_ms, dom_rays = (mc, own[0]) if mc >= ms_ else (ms_, own[1])
+        mcam = float(np.mean(k_cam))
+        # rays of each kind of launch: with the camera level in k_camera, the per-level closest / any-hit kernels only
+        # see the rays below it
+        fusedcam = mcam > 0
+        own = (float(st["rays_primary"] + st["rays_reflection"]) - (float(st["rays_primary"]) if fusedcam else 0.0),
+               float(st["rays_shadow"]) - ((rays_camera - float(st["rays_primary"])) if fusedcam else 0.0))
+        cands = [("k_camera", mcam, rays_camera if fusedcam else 0.0), ("k_trace<closest>", mc, own[0]), ("k_trace<anyhit>", ms_, own[1])]
+        dom, dom_ms, dom_rays = max(cands, key=lambda c: c[1])
         roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, n_tris, torch.cuda.get_device_properties(local).multi_processor_count,
                              clocks, peaks,
-                             extra=dict(kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
-                                        rays_by_kind=dict(closest=own[0], anyhit=own[1]),
+                             extra=dict(kernels_ms=dict(camera=mcam, closest=mc, anyhit=ms_, streaming=mo),
+                                        rays_by_kind=dict(camera=rays_camera if fusedcam else 0.0, closest=own[0], anyhit=own[1]),
                                         kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events on the launch "
                                                         f"stream, the frame as one tile group (each kernel alone on the GPU, k_coop counted with its "
-                                                        f"k_trace), {float(np.mean(ms_serial)):.4f} ms per step"))
+                                                        f"k_trace, k_coop_camera with k_camera), {float(np.mean(ms_serial)):.4f} ms per step"))
         line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
                     ms_per_step=total_ms / args.steps, higher_is_better=True, scaling="strong", vs_baseline=None,
                     dtype="f32", data="synthetic",
@@ -513,6 +524,8 @@ def run_multi_device(args, wl, rtp):
     info = scene.info()
     host = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory()
     host1 = torch.zeros(w * h * 3, dtype=torch.uint8).pin_memory()
+    st1 = one.render(w, h, max_depth=1, want=("rgb8",), out={"rgb8": host1.numpy().reshape(h, w, 3)})["stats"]
+    rays_camera = float(st1["rays_primary"] + st1["rays_shadow"])  # rays of the camera level (k_camera's launches), whole frame
     one.render(w, h, max_depth=md, want=("rgb8",), out={"rgb8": host1.numpy().reshape(h, w, 3)})
     one.close()
     flushes = [torch.empty(256 << 20, dtype=torch.uint8, device=torch.device("cuda", d)) for d in sorted(set(devices))]
@@ -545,22 +558,25 @@ def run_multi_device(args, wl, rtp):
         e2e_ms.append(1e3 * (time.perf_counter() - t0))
         ms_steps.append(st["ms_trace"])
     clocks = sampler.stop(t_begin, time.perf_counter())
-    k_closest, k_any, k_shade = [], [], []
+    k_closest, k_any, k_shade, k_cam = [], [], [], []
     for _ in range(min(args.steps, 20)):
         for f in flushes:
             f.zero_()
         sync_all()
         ps = frame(flags=rtp.RENDER_PROFILE)
-        k_closest.append(ps["ms_closest"]); k_any.append(ps["ms_anyhit"]); k_shade.append(ps["ms_shade"])
+        k_closest.append(ps["ms_closest"]); k_any.append(ps["ms_anyhit"]); k_shade.append(ps["ms_shade"]); k_cam.append(ps["ms_camera"])
     total_ms = sum(ms_steps)
     peaks = load_peaks()
-    mc, ms_, mo = float(np.mean(k_closest)), float(np.mean(k_any)), float(np.mean(k_shade))
-    dom = "k_trace<closest>" if mc >= ms_ else "k_trace<anyhit>"
-    dom_ms = max(mc, ms_)
-    dom_rays = float(st["rays_primary"] + st["rays_reflection"] if mc >= ms_ else st["rays_shadow"]) / n
+    mc, ms_, mo, mcam = float(np.mean(k_closest)), float(np.mean(k_any)), float(np.mean(k_shade)), float(np.mean(k_cam))
+    fusedcam = mcam > 0
+    own = (float(st["rays_primary"] + st["rays_reflection"]) - (float(st["rays_primary"]) if fusedcam else 0.0),
+           float(st["rays_shadow"]) - ((rays_camera - float(st["rays_primary"])) if fusedcam else 0.0))
+    cands = [("k_camera", mcam, rays_camera if fusedcam else 0.0), ("k_trace<closest>", mc, own[0]), ("k_trace<anyhit>", ms_, own[1])]
+    dom, dom_ms, dom_rays = max(cands, key=lambda c: c[1])
+    dom_rays /= n
     roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, info["n_triangles"],
                          torch.cuda.get_device_properties(devices[0]).multi_processor_count, clocks, peaks,
-                         extra=dict(kernels_ms=dict(closest=mc, anyhit=ms_, streaming=mo),
+                         extra=dict(kernels_ms=dict(camera=mcam, closest=mc, anyhit=ms_, streaming=mo),
                                     kernels_ms_from="more steps with RTP_RENDER_PROFILE: per-kernel CUDA events, max over the devices; "
                                                     "rays_per_launch_set = the frame's rays of that kind / devices"))
     cam_bytes = 4 * (12 + 4 + 2) + 24 * len(wl["lights"])

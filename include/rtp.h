@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define RTP_ABI_VERSION 6
+#define RTP_ABI_VERSION 7
 
 typedef enum rtp_status {
   RTP_OK = 0,
@@ -103,7 +103,8 @@ typedef struct rtp_stats {
   float ms_anyhit;  /* shadow-ray traversal (shadow)                                           */
   float ms_shade;   /* streaming kernels: Phong + reflection spawn of the camera level, resolve + image   */
   float ms_paths;   /* bounce levels >= 1, path by path in one persistent kernel (traceRay's recursion) */
-  int32_t reserved;
+  float ms_camera;  /* the camera level in one kernel (primary rays + their shadow rays + shading [+ image]); when it   */
+                    /* runs, ms_closest / ms_anyhit / ms_shade hold the levels below it and the fold only               */
 } rtp_stats;
 
 /* ---- lifetime ---------------------------------------------------------------------------- */

@@ -24,6 +24,8 @@ UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us":
 
 
 def kind_of(name):
+    if "k_camera" in name or "k_coop_camera" in name:
+        return "camera"
     if "Closest" in name:
         return "closest"
     if "Any" in name:
@@ -49,7 +51,7 @@ def main():
         return v * UNIT.get(U[i], 1.0)
 
     names = [r[ki] for r in data]
-    cam = [i for i, n in enumerate(names) if "FrameClosest<1>" in n and "k_trace" in n]
+    cam = [i for i, n in enumerate(names) if ("FrameClosest<1>" in n and "k_trace" in n) or "k_camera" in n]
     if len(cam) >= 2:
         lo, hi = cam[0], cam[1]
     elif cam:
@@ -90,7 +92,7 @@ def main():
                  "number), rays = the frame's rays of that kind (bench line).  Written by profiles/make_traffic.py from the "
                  "capture named in `from`; bench.py scales warp_inst and dram_bytes by rays(launch) / rays(entry).")
     ent = T.setdefault(workload, {})
-    knames = {"closest": "k_trace<closest>", "anyhit": "k_trace<anyhit>"}
+    knames = {"closest": "k_trace<closest>", "anyhit": "k_trace<anyhit>", "camera": "k_camera"}
     if not cam:
         knames = {"closest": "k_trace<RaysClosest>", "anyhit": "k_trace<RaysAny>"}
     for k, a in acc.items():

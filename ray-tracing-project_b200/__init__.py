@@ -53,7 +53,7 @@ class RtpStats(C.Structure):
                 ("hits", C.c_int64), ("ms_trace", C.c_float), ("ms_total", C.c_float),
                 ("kernel_launches", C.c_int32), ("n_bvh_nodes", C.c_int32), ("n_triangles", C.c_int32),
                 ("ms_closest", C.c_float), ("ms_anyhit", C.c_float), ("ms_shade", C.c_float),
-                ("ms_paths", C.c_float), ("reserved", C.c_int32)]
+                ("ms_paths", C.c_float), ("ms_camera", C.c_float)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}

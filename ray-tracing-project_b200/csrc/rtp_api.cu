@@ -188,6 +188,10 @@ struct rtp_scene {
   bool in_async_call = false;
   // RTP_L2_PERSIST=<MiB> (experiment, profiles/r02_design_items.md): that much of the L2 is set aside for persisting
   // lines and every stream a frame runs on gets an access-policy window over the head of the node array
+  // The camera level in one kernel (k_camera) or as separate closest / any-hit / shading launches: RTP_FUSED=1 / 0 forces
+  // one of them (A/B runs, parity suite), -1 = by size (enqueue_frame)
+  int fused = -1;
+  int fused_px = 1300000;  // RTP_FUSED_PX: scenes that spill out of the L2 fuse up to this many pixel x light pairs per rank
   int l2_persist_mb = 0;
   std::vector<cudaStream_t> l2_streams;  // streams that carry the window already
   int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
@@ -253,6 +257,8 @@ int init_device_side(rtp_scene *s) {
   if (const char *te = std::getenv("RTP_PATHS_PX_SMALL")) s->paths_px_small = std::atoi(te);
   if (const char *pe = std::getenv("RTP_PATHS_FROM")) s->paths_from = std::atoi(pe);
   if (const char *ge = std::getenv("RTP_GROUPS")) s->groups = std::min(std::max(std::atoi(ge), 0), kMaxGroups);
+  if (const char *fe = std::getenv("RTP_FUSED")) s->fused = std::atoi(fe);
+  if (const char *fe = std::getenv("RTP_FUSED_PX")) s->fused_px = std::atoi(fe);
   if (const char *le = std::getenv("RTP_L2_PERSIST")) {
     s->l2_persist_mb = std::max(std::atoi(le), 0);
     if (s->l2_persist_mb) CK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)s->l2_persist_mb << 20));
@@ -780,6 +786,7 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     gp[g] = G == 1 ? p : group_params(p, g, tile0[g], tile0[g + 1]);
     gc[g] = s->cfg;
     gc[g].park_cap = s->cfg.park_cap / G;
+    gc[g].groups = G;
     gc[g].park_slots = s->cfg.park_slots + (size_t)g * gc[g].park_cap * (kParkSlotBytes / sizeof(int));
     gs[g] = g == 0 ? st : s->gstream[g];
     if (s->l2_persist_mb) { int lrc = apply_l2_window(s, gs[g]); if (lrc) return lrc; }
@@ -802,7 +809,21 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   // the higher floor per level, hence the higher threshold.  RTP_DEEP=paths|wavefront forces one of them.
   const bool use_paths = s->deep_mode == 1 || (s->deep_mode < 0 && p.n_px <= (s->cfg.scene_exceeds_l2 ? s->paths_px_big : s->paths_px_small));
   const int wave_levels = use_paths ? std::min(p.max_depth, std::max(1, s->paths_from)) : p.max_depth;
+  // The camera level in one kernel (k_camera) or as separate launches - measured on B200 (profiles/r02_camera.md).  On a
+  // scene that fits the L2 nothing is parked and the fused kernel is level or ahead at every size (C2 0.575 / 0.576 ms,
+  // a 1/8 share 0.269 / 0.283).  On a scene that spills out of it the separate launches win the big frames - their tails
+  // overlap across the tile groups, and a parked PIXEL costs k_coop_camera its shadow rays and shading on top of the
+  // primary ray (C3 0.709 / 0.646 ms) - and the fused kernel wins once a rank's share is small: one launch instead of
+  // three dependent ones, each as long as its longest ray (C3 1/2 share 0.391 / 0.420, 1/4 0.252 / 0.278, 1/8 0.172 /
+  // 0.206 ms); with four lights the crossover comes earlier (C4 1/8 share, 1.0 M pixels: 1.60 / 1.58).
+  const bool fused = camera_fusable(p) &&
+                     (s->fused >= 0 ? s->fused != 0
+                                    : (!s->cfg.scene_exceeds_l2 || (long long)p.n_px * std::max(p.S.n_lights, 1) <= s->fused_px));
   for (int d = 0; d < wave_levels; ++d) {
+    if (d == 0 && fused) {
+      for (int g = 0; g < G; ++g) { CK(mark(4)); n += launch_camera(gp[g], gc[g], gs[g]); CK(stamp("camera", g, d, gs[g])); }
+      continue;
+    }
     for (int g = 0; g < G; ++g) { CK(mark(0)); n += launch_closest(gp[g], d, gc[g], gs[g]); CK(stamp("closest", g, d, gs[g])); }
     for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit(gp[g], d, gc[g], gs[g]); CK(stamp("anyhit", g, d, gs[g])); }
     if (p.max_depth > 1)  // max_depth 1: the resolve kernel shades the only level itself
@@ -811,8 +832,10 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   if (wave_levels < p.max_depth)
     for (int g = 0; g < G; ++g) { CK(mark(3)); launch_paths(gp[g], wave_levels, gc[g], gs[g]); ++n; CK(stamp("paths", g, wave_levels, gs[g])); }
   for (int g = 0; g < G; ++g) {
-    CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
-    CK(stamp("resolve", g, 0, gs[g]));
+    if (!(fused && p.max_depth == 1)) {  // k_camera has written the image of a one-level frame itself
+      CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
+      CK(stamp("resolve", g, 0, gs[g]));
+    }
     CK(after_group(g, tile0[g], tile0[g + 1], gs[g]));
   }
   CK(mark(-1));
@@ -876,7 +899,7 @@ int read_stats(rtp_scene *s, rtp_stats *st, cudaStream_t stream) {
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, s->kev[i], s->kev[i + 1]));
     const int kind = s->kev_kind[(size_t)i];
-    (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : kind == 3 ? st->ms_paths : st->ms_shade) += ms;
+    (kind == 0 ? st->ms_closest : kind == 1 ? st->ms_anyhit : kind == 3 ? st->ms_paths : kind == 4 ? st->ms_camera : st->ms_shade) += ms;
   }
   stats_from_counters(s, hg, G, s->last_primary, s->last_depth, s->last_lights, st);
   return RTP_OK;
@@ -1241,6 +1264,7 @@ int rtp_render(rtp_scene *s, const rtp_render_opts *o, float *rgb, uint8_t *rgb8
       st->ms_anyhit = std::max(st->ms_anyhit, ps.ms_anyhit);
       st->ms_shade = std::max(st->ms_shade, ps.ms_shade);
       st->ms_paths = std::max(st->ms_paths, ps.ms_paths);
+      st->ms_camera = std::max(st->ms_camera, ps.ms_camera);
       st->kernel_launches += p->last_launches;
     }
     CK(cudaEventElapsedTime(&st->ms_trace, s->ev[0], s->ev[1]));  // one GPU: includes the overlapped band copies

@@ -248,11 +248,13 @@ RTP_HD void trav_init(Trav &t, v3 o, v3 d, int *stack) {
 // paid on entry, every time).
 // MODE 0: closest hit, 1: any hit (compile-time), 2: per ray at run time (t.any) - the deep-path kernel, whose warps hold
 // closest-hit and shadow rays side by side; same arithmetic and the same decisions per ray in every mode.
+// max_trips: inner nodes a step may visit (<= kMaxNodesPerStep).  Lanes that reach their leaf early idle until the
+// slowest lane of the warp leaves the node loop, so scattered rays want a short leash (k_trace's step_nodes).
 template <int MODE, class BoxOrigin>
-RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_origin) {
+RTP_HD bool trav_step(const DeviceScene &S, Trav &t, int *stack, BoxOrigin box_origin, const int max_trips = kMaxNodesPerStep) {
   const bool ANY = MODE == 2 ? t.any : MODE == 1;
   int node = t.node, sp = t.sp;
-  for (int trip = 0; node >= 0 && node != kSentinel && trip < kMaxNodesPerStep; ++trip) {
+  for (int trip = 0; node >= 0 && node != kSentinel && trip < max_trips; ++trip) {
     const float4 *Np = S.nodes + 4 * (size_t)node;
     RTP_CHECK_DEV(node < S.n_nodes, 1, node, S.n_nodes);
     RTP_STAT(nodes);

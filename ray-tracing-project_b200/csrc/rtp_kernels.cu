@@ -21,6 +21,7 @@
 // and triangles.  FP32 CUDA cores only; no tensor cores (not a dense contraction).
 #include "rtp_kernels.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <mutex>
 
@@ -236,6 +237,7 @@ struct ParkList {
   int cap;      // slots available; a ray that finds the list full simply carries on
   int budget;   // steps a warp spends on a batch before its last lanes count as stragglers (huge = never park)
   int lanes;    // ... and at most this many lanes still hold a ray
+  int step_nodes;  // inner nodes per trav_step (kMaxNodesPerStep for coherent batches; RTP_STEP_NODES for scattered rays)
 };
 
 // Finishes the (warp-uniform) ray in t with all 32 lanes, starting from the n pending entries in ws;
@@ -445,7 +447,7 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, co
       age = 0;
       continue;
     }
-    if (have && t.node != kSentinel) trav_step<Job::kAny ? 1 : 0>(job.S, t, stack, [&] { return job.box_origin(q, t); });
+    if (have && t.node != kSentinel) trav_step<Job::kAny ? 1 : 0>(job.S, t, stack, [&] { return job.box_origin(q, t); }, pl.step_nodes);
   }
 #ifdef RTP_TRACE_TIMING
   if (lane == 0) {
@@ -513,7 +515,9 @@ __global__ void __launch_bounds__(256) k_raygen(const FrameParams p) {
 
 // calculateColor for hit record h (flyscene.cpp:603-614): interpolated normal (flyscene.cpp:572-600), Phong over the
 // unshadowed lights, clamped.  ks_out: the material's specular colour (the reflection weight of SURVEY.md Q5).
-__device__ __forceinline__ v3 shade_hit(const FrameParams &p, int h, v3 o, v3 P, int slot, v3 &normal, float4 &ks_out) {
+// shadowed(li): the outcome of shadow() for this hit and light li.
+template <class Shadowed>
+__device__ __forceinline__ v3 shade_hit_with(const FrameParams &p, Shadowed shadowed, v3 o, v3 P, int slot, v3 &normal, float4 &ks_out) {
   normal = interpolate_normal_slot(p.S, slot, P);
   const unsigned mat = (unsigned)f2i(__ldg(p.S.tris + 4 * (size_t)slot + 2).w) & kTriMatMask;
   const float4 m0 = __ldg(p.S.materials + 3 * mat), m1 = __ldg(p.S.materials + 3 * mat + 1),
@@ -521,7 +525,7 @@ __device__ __forceinline__ v3 shade_hit(const FrameParams &p, int h, v3 o, v3 P,
   const int n_lights = p.S.n_lights;
   v3 sum = mk3(0.f, 0.f, 0.f);
   for (int li = 0; li < n_lights; ++li) {  // calculateColor, flyscene.cpp:606-612
-    if (p.occl[(size_t)h * n_lights + li]) continue;  // shadowed: contributes nothing (:543-545)
+    if (shadowed(li)) continue;  // shadowed: contributes nothing (:543-545)
     const float4 l0 = __ldg(p.S.lights + 2 * li), l1 = __ldg(p.S.lights + 2 * li + 1);
     v3 L = xyz(l0);
     if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // :607
@@ -529,6 +533,10 @@ __device__ __forceinline__ v3 shade_hit(const FrameParams &p, int h, v3 o, v3 P,
   }
   ks_out = m2;
   return mk3(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z));
+}
+__device__ __forceinline__ v3 shade_hit(const FrameParams &p, int h, v3 o, v3 P, int slot, v3 &normal, float4 &ks_out) {
+  const int n_lights = p.S.n_lights;
+  return shade_hit_with(p, [&](int li) { return p.occl[(size_t)h * n_lights + li] != 0; }, o, P, slot, normal, ks_out);
 }
 
 // origin of path q at `depth` (camera frames: the eye at depth 0; otherwise the level's ray list)
@@ -825,6 +833,299 @@ __global__ void __launch_bounds__(256) k_resolve_image(const FrameParams p) {
   if (valid && p.img_hit) p.img_hit[idx] = f2i(out.w);
 }
 
+// ---- the camera level of a frame in ONE kernel -----------------------------------------------------------------------
+// k_trace<FrameClosest> -> (k_coop) -> k_trace<FrameAny> -> (k_coop) -> k_accum / k_resolve_image are dependent launches,
+// each with a latency-bound tail (its last batches of dependent node fetches leave most SMs idle), and the pixels' hit
+// records travel through HBM between them (hit_slot, pbuf, dbuf, occl: ~100 B per pixel).  k_camera runs the whole
+// camera level of traceRay (flyscene.cpp:299-371 at depth 0) per warp batch instead: a warp takes an 8x4-pixel footprint,
+// generates the 32 primary rays, finds their closest hits (trav_step<0>), then sends the 32 shadow rays towards light 0,
+// light 1, ... (trav_step<1>), shades its pixels and - max_depth 1 - stores them straight into the image (which may be
+// GPU 0's, over NVLink); with max_depth > 1 it leaves the level-0 records the fold needs (direct, ksdeep, primface) and
+// appends the reflection rays to level 1's ray list.  The phases are batch-synchronous inside the warp, as in k_trace's
+// batch mode - neighbouring pixels stay together, the rays of a phase are coherent - but different warps are in
+// different phases, so the only tail left is the frame's.  The hit record of a pixel (P, triangle slot, occlusion bits)
+// never leaves the SM: shared memory between the phases.  Same functions and arithmetic as the per-phase kernels
+// (RTP_FUSED=0 selects those; the parity suite runs under both).
+// Stragglers are parked as in k_trace; k_coop_camera finishes a parked PIXEL with a whole warp: the rest of its primary
+// ray or of its shadow ray towards light li (coop_trace from the saved stack), the remaining lights (coop_trace from the
+// root), shading, output.  Parked record (kParkInts ints): [0] (pixel + 1) | li << 24 | kCamAnyFlag | careful << 31,
+// primary ray: [1..3] best t / rank / slot so far; shadow ray: [1..3] the hit point P, [70] its triangle slot, [71] the
+// occlusion bits of lights < li; [4] n, [5..] the pending stack.
+constexpr int kCamAnyFlag = 1 << 29;
+constexpr int kCamMaxLights = 32;         // occlusion bits of a pixel live in one register
+constexpr int kCamMaxPixels = 1 << 24;    // pixel id field of a parked record
+struct CamPark {
+  int *slots, *ctr;
+  int cap;
+  int budget, lanes;          // primary rays: steps a warp spends on a batch before the rays still running are parked
+  int budget_any, lanes_any;  // shadow rays
+};
+
+// pixel q of this rank's tile-major pixel list -> image coordinates; false: tile padding outside the image
+__device__ __forceinline__ bool cam_pixel(const FrameParams &p, int q, int &i, int &j) {
+  const int tile = __ldg(p.tile_ids + (q >> 10));
+  int x, y;
+  tile_pixel(q & (kTilePixels - 1), x, y);
+  i = (tile % p.tiles_x) * kTileDim + x;
+  j = (tile / p.tiles_x) * kTileDim + y;
+  return i < p.width && j < p.height;
+}
+
+__device__ __forceinline__ v3 cam_light_dir(const DeviceScene &S, int li, v3 P) {
+  const float4 l0 = __ldg(S.lights + 2 * li);
+  v3 L = xyz(l0);
+  if (l0.w == 0.f) L = vneg(vnormalized(vsub(P, L)));  // flyscene.cpp:607
+  return L;
+}
+
+__device__ __forceinline__ bool cam_park(const CamPark &pk, int head, int a1, int a2, int a3, const Trav &t, const int *stack,
+                                         int x0, int x1) {
+  const int at = atomicAdd(pk.ctr, 1);
+  if (at >= pk.cap) return false;  // list full: the ray simply carries on
+  int *e = pk.slots + (size_t)at * kParkInts;
+  e[0] = head; e[1] = a1; e[2] = a2; e[3] = a3;
+  int n = 0;
+  for (int i = 1; i <= t.sp; ++i) e[5 + n++] = RTP_STK(stack, i);
+  if (t.node != kSentinel) e[5 + n++] = t.node;
+  RTP_CHECK(5 + n <= kParkInts - 2, 25, 5 + n, kParkInts - 2);
+  e[4] = n;
+  e[kParkInts - 2] = x0; e[kParkInts - 1] = x1;
+  return true;
+}
+
+// What is left of a camera pixel once its rays are traced: calculateColor over the unshadowed lights (occ: bit li =
+// shadow(P, light li)), then - DEPTH1 - the fold of the only level (clamp(direct + 0 * ks), as shade_pixel_depth1) and the
+// outputs of k_resolve / k_resolve_image; otherwise the level-0 records of the fold and the reflection ray (o2, r) of
+// flyscene.cpp:355-363: returns true when that ray has to be appended to level 1's list (the caller compacts).
+template <bool DEPTH1>
+__device__ __forceinline__ bool camera_finish(const FrameParams &p, int q, int i, int j, bool valid, bool hit, v3 P, int slot,
+                                              unsigned occ, v3 &o2, v3 &r) {
+  const int face = !valid ? -2 : hit ? __ldg(p.S.face_of + slot) : -1;
+  float4 ks = make_float4(0.f, 0.f, 0.f, 0.f);
+  v3 c = mk3(0.f, 0.f, 0.f), normal = c;
+  if (hit)
+    c = shade_hit_with(p, [&](int li) { return ((occ >> li) & 1u) != 0u; }, mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]), P, slot,
+                       normal, ks);
+  if (DEPTH1) {
+    float4 out = make_float4(0.f, 0.f, 0.f, i2f(-1));                    // pixel outside the image
+    if (valid && !hit) out = make_float4(p.bg[0], p.bg[1], p.bg[2], i2f(-1));  // flyscene.cpp:327-330
+    if (hit) out = make_float4(clamp01(fadd(c.x, fmul(0.f, ks.x))), clamp01(fadd(c.y, fmul(0.f, ks.y))),
+                               clamp01(fadd(c.z, fmul(0.f, ks.z))), i2f(face));
+    if (p.fb) p.fb[q] = out;
+    if (valid) {
+      const size_t idx = (size_t)j * p.width + i;
+      RTP_CHECK(idx < (size_t)p.width * p.height, 34, idx, p.width * p.height);
+      if (p.img_rgb) { p.img_rgb[3 * idx] = out.x; p.img_rgb[3 * idx + 1] = out.y; p.img_rgb[3 * idx + 2] = out.z; }
+      if (p.img_rgb8) {  // the 8 lanes of a footprint row store 24 consecutive bytes
+        p.img_rgb8[3 * idx] = quantise(out.x); p.img_rgb8[3 * idx + 1] = quantise(out.y); p.img_rgb8[3 * idx + 2] = quantise(out.z);
+      }
+      if (p.img_hit) p.img_hit[idx] = f2i(out.w);
+    }
+    return false;
+  }
+  p.primface[q] = face;
+  if (!hit) {
+    p.ksdeep[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    return false;
+  }
+  p.direct[q] = make_float4(c.x, c.y, c.z, 0.f);  // level 0
+  p.ksdeep[q] = make_float4(ks.x, ks.y, ks.z, i2f(1));
+  r = reflect_dir(primary_dir(p.cam, i, j), normal);  // :361
+  o2 = vadd(P, vmuls(r, (float)0.001));               // :362
+  return true;
+}
+
+template <bool DEPTH1>
+__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_camera(const FrameParams p, const CamPark pk) {
+  __shared__ float s_P[3][128];
+  __shared__ int s_slot[128];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const DeviceScene &S = p.S;
+  const int n_lights = S.n_lights;
+  int *const cursor = p.counters + kCtrFetchClosest;
+  int stack[kStackSize];
+  for (;;) {
+    int base = 0;
+    if (lane == 0) base = atomicAdd(cursor, 32);
+    base = __shfl_sync(kFull, base, 0);
+    if (base >= p.n_px) break;  // n_px is a multiple of 1024: whole batches
+    const int q = base + lane;
+    Trav t;
+    t.node = kSentinel;
+    t.sbest = -1;
+    bool have;
+    {
+      int i, j;
+      have = cam_pixel(p, q, i, j);
+      if (have) trav_init(t, mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]), primary_dir(p.cam, i, j), stack);
+    }
+    // ---- phase A: calculateMinimumFace for the 32 primary rays (flyscene.cpp:373-396)
+    bool parked = false;
+    for (int age = 0;;) {
+      const unsigned act = __ballot_sync(kFull, have && t.node != kSentinel);
+      if (act == 0) {  // all traversals have ended: the deferred BoundingBox check of the winners, together
+        const bool again = have && closest_needs_rerun(S, t, stack);  // careful re-run from the root
+        if (!__any_sync(kFull, again)) break;
+        continue;
+      }
+      if (++age > pk.budget && __popc(act) <= pk.lanes) {
+        if (have && t.node != kSentinel &&
+            cam_park(pk, (q + 1) | (t.careful ? (int)0x80000000 : 0), f2i(t.tbest), (int)t.rbest, t.sbest, t, stack, 0, 0)) {
+          have = false;
+          parked = true;
+        }
+        age = 0;
+        continue;
+      }
+      if (have && t.node != kSentinel) trav_step<0>(S, t, stack, [&] { return t.o; });
+    }
+    const bool hit = have && t.sbest >= 0;
+    {
+      const unsigned m = __ballot_sync(kFull, hit);
+      if (m && lane == __ffs(m) - 1) atomicAdd(p.counters + kCtrHits, __popc(m));
+    }
+    if (hit) {
+      RTP_CHECK((unsigned)t.sbest < (unsigned)S.n_tris, 12, t.sbest, S.n_tris);
+      const v3 P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
+      s_P[0][tid] = P.x; s_P[1][tid] = P.y; s_P[2][tid] = P.z;
+      s_slot[tid] = t.sbest;
+    }
+    // ---- phase B: shadow(P, light) for the batch, light after light (flyscene.cpp:510-526,606-612)
+    unsigned occ = 0;
+    for (int li = 0; li < n_lights; ++li) {
+      bool run = hit && !parked;
+      if (!__any_sync(kFull, run)) break;
+      t.node = kSentinel;
+      if (run) {
+        const v3 P = mk3(s_P[0][tid], s_P[1][tid], s_P[2][tid]);
+        const v3 L = cam_light_dir(S, li, P);
+        trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);  // flyscene.cpp:512
+      }
+      for (int age = 0;;) {
+        const unsigned act = __ballot_sync(kFull, run && t.node != kSentinel);
+        if (act == 0) break;
+        if (++age > pk.budget_any && __popc(act) <= pk.lanes_any) {
+          if (run && t.node != kSentinel &&
+              cam_park(pk, (q + 1) | (li << 24) | kCamAnyFlag, f2i(s_P[0][tid]), f2i(s_P[1][tid]), f2i(s_P[2][tid]), t, stack,
+                       s_slot[tid], (int)occ)) {
+            run = false;
+            parked = true;
+          }
+          age = 0;
+          continue;
+        }
+        if (run && t.node != kSentinel)
+          trav_step<1>(S, t, stack, [&] { return mk3(s_P[0][tid], s_P[1][tid], s_P[2][tid]); });
+      }
+      if (run && t.sbest >= 0) occ |= 1u << li;
+    }
+    // ---- phase C: shading and output (parked pixels: k_coop_camera)
+    v3 o2 = mk3(0.f, 0.f, 0.f), r = o2;
+    bool spawn = false;
+    if (!parked) {
+      int i, j;
+      const bool valid = cam_pixel(p, q, i, j);
+      const v3 P = hit ? mk3(s_P[0][tid], s_P[1][tid], s_P[2][tid]) : o2;
+      spawn = camera_finish<DEPTH1>(p, q, i, j, valid, hit, P, hit ? s_slot[tid] : -1, occ, o2, r);
+    }
+    if (!DEPTH1) {
+      const unsigned m = __ballot_sync(kFull, spawn);
+      if (m) {
+        const int leader = __ffs(m) - 1;
+        int dst = 0;
+        if (lane == leader) dst = atomicAdd(p.counters + kCtrPaths + 1, __popc(m));
+        dst = __shfl_sync(kFull, dst, leader) + __popc(m & ((1u << lane) - 1u));
+        if (spawn) {
+          RTP_CHECK((unsigned)dst < (unsigned)p.n_px, 30, dst, p.n_px);
+          p.ray_o[1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(q));
+          p.ray_d[1][dst] = make_float4(r.x, r.y, r.z, 1.f);
+        }
+      }
+    }
+  }
+}
+
+// Finishes the pixels k_camera parked, one warp per pixel.
+template <bool DEPTH1>
+__global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, const CamPark pk) {
+  __shared__ int s_ws[4][kCoopStack];
+  int *const ws = s_ws[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  const DeviceScene &S = p.S;
+  const int n_lights = S.n_lights;
+  const int n_parked = min(*pk.ctr, pk.cap);
+  int stack[1];  // trav_init / closest_needs_rerun write stack[0] only
+  for (;;) {
+    int k = 0;
+    if (lane == 0) k = atomicAdd(pk.ctr + 1, 1);
+    k = __shfl_sync(kFull, k, 0);
+    if (k >= n_parked) break;
+    const int *e = pk.slots + (size_t)k * kParkInts;
+    const int head = e[0];
+    const int q = (head & (kCamMaxPixels - 1)) - 1;
+    RTP_CHECK((unsigned)q < (unsigned)p.n_px, 26, q, p.n_px);
+    int i, j;
+    cam_pixel(p, q, i, j);  // a parked pixel is inside the image
+    int n = e[4];
+    RTP_CHECK(n >= 0 && 5 + n <= kParkInts - 2, 24, n, kParkInts - 7);
+    for (int x = lane; x < n; x += 32) ws[x] = e[5 + x];
+    __syncwarp();
+    Trav t;
+    v3 P = mk3(0.f, 0.f, 0.f);
+    int slot = -1, li = 0;
+    unsigned occ = 0;
+    bool hit;
+    if (!(head & kCamAnyFlag)) {  // the pixel's primary ray: the same ray in every lane
+      trav_init(t, mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]), primary_dir(p.cam, i, j), stack);
+      t.tbest = i2f(e[1]); t.rbest = (unsigned)e[2]; t.sbest = e[3]; t.careful = head < 0;
+      for (;;) {
+        coop_trace<false>(S, t, t.o, ws, n);
+        if (!closest_needs_rerun(S, t, stack)) break;
+        if (lane == 0) ws[0] = 0;  // the winner's box failed: start over from the root, careful
+        n = 1;
+        __syncwarp();
+      }
+      hit = t.sbest >= 0;
+      if (hit) {
+        P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
+        slot = t.sbest;
+        if (lane == 0) atomicAdd(p.counters + kCtrHits, 1);
+      }
+    } else {  // its shadow ray towards light li: hit point, slot and the bits of the lights before it come with the record
+      hit = true;
+      P = mk3(i2f(e[1]), i2f(e[2]), i2f(e[3]));
+      slot = e[kParkInts - 2];
+      occ = (unsigned)e[kParkInts - 1];
+      li = (head >> 24) & (kCamMaxLights - 1);
+      const v3 L = cam_light_dir(S, li, P);
+      trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
+      coop_trace<true>(S, t, P, ws, n);
+      if (t.sbest >= 0) occ |= 1u << li;
+      ++li;
+    }
+    if (hit)
+      for (; li < n_lights; ++li) {  // the lights that are left, each from the root
+        const v3 L = cam_light_dir(S, li, P);
+        trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
+        __syncwarp();
+        if (lane == 0) ws[0] = 0;
+        __syncwarp();
+        coop_trace<true>(S, t, P, ws, 1);
+        if (t.sbest >= 0) occ |= 1u << li;
+      }
+    if (lane == 0) {
+      v3 o2, r;
+      if (camera_finish<DEPTH1>(p, q, i, j, true, hit, P, slot, occ, o2, r)) {
+        const int dst = atomicAdd(p.counters + kCtrPaths + 1, 1);
+        RTP_CHECK((unsigned)dst < (unsigned)p.n_px, 30, dst, p.n_px);
+        p.ray_o[1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(q));
+        p.ray_d[1][dst] = make_float4(r.x, r.y, r.z, 1.f);
+      }
+    }
+    __syncwarp();
+  }
+}
+
 __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile,
                                                 int width, int height, int tiles_x, int world, int only_rank,
                                                 float *rgb, unsigned char *rgb8, int *hit) {
@@ -895,33 +1196,39 @@ int g_refill = -2;  // RTP_REFILL overrides the per-launch policy below (tuning 
 // the launch is as long as its longest ray (1/8 share 0.255 -> 0.23 ms) - in a full-frame launch their k_coop pass
 // costs more than the tail it removes (0.735 -> 0.79 ms).
 int g_budget = 6;       // RTP_BUDGET: steps a warp spends on a batch before the rays still running are parked (0: never)
+bool g_budget_from_env = false;
 int g_park_lanes = 32;  // RTP_PARK_LANES: ... if at most this many lanes are still running
 int g_park_any = 0;     // RTP_PARK_ANY=1: park shadow rays in every launch
 int g_any_small = 400000;  // RTP_ANY_SMALL: ... or in launches over at most this many paths
 int g_budget_any = 6;   // RTP_BUDGET_ANY: step budget of shadow-ray launches (a step of an unoccluded ray is 32 nodes)
 int g_park_lanes_any = 32;
 int g_park_small = 0;   // RTP_PARK_SMALL=1: park on L2-resident scenes too
+int g_step_nodes = kMaxNodesPerStep;  // RTP_STEP_NODES: inner nodes per step of scattered-ray launches (lane refill mode)
 
 // Refill policy: a warp refills its idle lanes from the global ray list when fewer than `refill`
 // lanes still hold a ray.  Coherent waves (camera rays, their point-light shadow rays) run
 // fastest in batch mode (refill only when the whole warp is idle: neighbouring pixels stay
 // together, measured +6% on C3); scattered waves (reflection levels, caller-supplied rays)
 // keep at least 24 lanes busy.
+void read_policy_env() {
+  if (g_refill != -2) return;
+  const char *e = std::getenv("RTP_REFILL");
+  g_refill = e ? std::atoi(e) : -1;
+  if ((e = std::getenv("RTP_BUDGET"))) { g_budget = g_budget_any = std::atoi(e); g_budget_from_env = true; }
+  if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = g_park_lanes_any = std::atoi(e);
+  if ((e = std::getenv("RTP_PARK_ANY"))) g_park_any = std::atoi(e);
+  if ((e = std::getenv("RTP_ANY_SMALL"))) g_any_small = std::atoi(e);
+  if ((e = std::getenv("RTP_BUDGET_ANY"))) g_budget_any = std::atoi(e);
+  if ((e = std::getenv("RTP_PARK_LANES_ANY"))) g_park_lanes_any = std::atoi(e);
+  if ((e = std::getenv("RTP_PARK_SMALL"))) g_park_small = std::atoi(e);
+  if ((e = std::getenv("RTP_STEP_NODES"))) g_step_nodes = std::min(std::max(std::atoi(e), 1), kMaxNodesPerStep);
+}
+
 template <class Job>
 int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters, int launch_slot, bool coherent,
                  long long n_paths, cudaStream_t st) {
   const int threads = cfg.threads;
-  if (g_refill == -2) {
-    const char *e = std::getenv("RTP_REFILL");
-    g_refill = e ? std::atoi(e) : -1;
-    if ((e = std::getenv("RTP_BUDGET"))) g_budget = g_budget_any = std::atoi(e);
-    if ((e = std::getenv("RTP_PARK_LANES"))) g_park_lanes = g_park_lanes_any = std::atoi(e);
-    if ((e = std::getenv("RTP_PARK_ANY"))) g_park_any = std::atoi(e);
-    if ((e = std::getenv("RTP_ANY_SMALL"))) g_any_small = std::atoi(e);
-    if ((e = std::getenv("RTP_BUDGET_ANY"))) g_budget_any = std::atoi(e);
-    if ((e = std::getenv("RTP_PARK_LANES_ANY"))) g_park_lanes_any = std::atoi(e);
-    if ((e = std::getenv("RTP_PARK_SMALL"))) g_park_small = std::atoi(e);
-  }
+  read_policy_env();
   static int refill_any = -2, refill_closest = -2;
   if (refill_any == -2) {
     const char *e = std::getenv("RTP_REFILL_ANY");
@@ -939,6 +1246,8 @@ int launch_trace(const Job &job, int blocks, const LaunchCfg &cfg, int *counters
                     (cfg.scene_exceeds_l2 || g_park_small);
   pl.budget = park ? (Job::kAny ? g_budget_any : g_budget) : 0x3fffffff;
   pl.lanes = Job::kAny ? g_park_lanes_any : g_park_lanes;
+  pl.step_nodes = coherent ? kMaxNodesPerStep : g_step_nodes;
+  if (pl.step_nodes < kMaxNodesPerStep && pl.budget < 0x3fffffff) pl.budget *= kMaxNodesPerStep / pl.step_nodes;  // the budget is in 32-node steps
   if (refill <= 1) k_trace<Job, 1><<<blocks, threads, 0, st>>>(job, pl);
   else if (refill <= 8) k_trace<Job, 8><<<blocks, threads, 0, st>>>(job, pl);
   else k_trace<Job, 24><<<blocks, threads, 0, st>>>(job, pl);
@@ -964,6 +1273,9 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   int b2 = 1;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_paths<24>, 128, 0);
   cfg.blocks_paths = sms * (b2 > 0 ? b2 : 1);
+  int b3 = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_camera<true>, 128, 0);
+  cfg.blocks_camera = sms * (b3 > 0 ? b3 : 1);
   cfg.blocks_coop = sms * 2;
   if (const char *e = std::getenv("RTP_COOP_BLOCKS")) cfg.blocks_coop = sms * std::max(1, std::atoi(e));  // per SM (tuning runs)
 }
@@ -1019,6 +1331,34 @@ static int launch_anyhit_t(const FrameParams &p, int depth, const LaunchCfg &cfg
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
   if (depth == 0 && !p.user_rays) return launch_anyhit_t<true>(p, depth, cfg, st);  // camera level: dense records
   return launch_anyhit_t<false>(p, depth, cfg, st);
+}
+
+bool camera_fusable(const FrameParams &p) {
+  return !p.user_rays && p.tile_ids && p.S.n_lights <= kCamMaxLights && p.n_px < kCamMaxPixels;
+}
+
+int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st) {
+  read_policy_env();
+  CamPark pk;
+  pk.slots = cfg.park_slots;
+  pk.ctr = p.counters + kCtrPark;  // launch slot 0
+  pk.cap = cfg.park_cap;
+  // the straggler policy of launch_trace: closest-hit rays park on scenes that spill out of the L2, shadow rays only
+  // when the launch is small as well
+  const bool park = g_budget > 0 && cfg.park_slots && (cfg.scene_exceeds_l2 || g_park_small);
+  const bool park_any = park && (g_park_any || p.n_px <= g_any_small);
+  // a parked pixel is dear here (k_coop_camera also traces its shadow rays and shades it): above 600 k pixels per launch
+  // sequence only the really long rays are parked (C3 1/2 share: 0.441 ms at 6 steps, 0.391 at 14; 1/8 share: 0.172 / 0.235)
+  pk.budget = park ? (g_budget_from_env || p.n_px * cfg.groups <= 600000 ? g_budget : 2 * g_budget) : 0x3fffffff;
+  pk.lanes = g_park_lanes;
+  pk.budget_any = park_any ? g_budget_any : 0x3fffffff;
+  pk.lanes_any = g_park_lanes_any;
+  if (p.max_depth == 1) k_camera<true><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
+  else k_camera<false><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
+  if (!park) return 1;
+  if (p.max_depth == 1) k_coop_camera<true><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
+  else k_coop_camera<false><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
+  return 2;
 }
 
 void launch_paths(const FrameParams &p, int first_depth, const LaunchCfg &cfg, cudaStream_t st) {

@@ -46,9 +46,10 @@ struct FrameParams {
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, blocks_camera = 0, threads = 128;
   int *park_slots = nullptr;  // parked-ray list storage (park_cap * kParkSlotBytes), owned by the scene
   int park_cap = 0;
+  int groups = 1;  // tile groups of the frame this launch belongs to (a group's n_px x groups = the rank's pixels)
   bool scene_exceeds_l2 = false;  // nodes + triangles larger than half the L2: traversal chains run on cold lines
 };
 void query_launch_cfg(int device, LaunchCfg &cfg);
@@ -61,6 +62,12 @@ void launch_raygen(const FrameParams &p, cudaStream_t st);
 int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
 // shadow() for every (hit, light) pair (flyscene.cpp:510-526)
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// The camera level of a frame in one kernel (k_camera: primary rays, their shadow rays, shading, and - max_depth 1 - the
+// image; max_depth > 1: the level-0 records and level 1's ray list), plus k_coop_camera for parked pixels: replaces
+// launch_closest(0) + launch_anyhit(0) + launch_accum(0) and, at max_depth 1, launch_resolve.  camera_fusable: the frame
+// qualifies (camera rays, at most 32 lights, fewer than 2^24 pixels per launch).  Returns the kernels launched.
+bool camera_fusable(const FrameParams &p);
+int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st);
 // every bounce level from first_depth on, path by path, in one persistent kernel (k_paths): replaces the per-level
 // launch_closest / launch_anyhit / launch_accum sequence below the camera level
 void launch_paths(const FrameParams &p, int first_depth, const LaunchCfg &cfg, cudaStream_t st);

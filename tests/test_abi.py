@@ -23,7 +23,7 @@ def test_header_symbols_are_exported(rtp):
     for n in names:
         assert hasattr(L, n), f"{n} declared in include/rtp.h but not exported"
     assert sorted(rtp.EXPORTS) == names
-    assert L.rtp_abi_version() == 6
+    assert L.rtp_abi_version() == 7
 
 
 def test_struct_sizes_match_header(rtp):

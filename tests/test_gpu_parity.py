@@ -294,3 +294,28 @@ def test_path_kernel_equals_the_per_level_kernels(rtp, name, monkeypatch):
     for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits"):
         assert a["stats"][k] == b["stats"][k], k
     assert a["stats"]["kernel_launches"] < b["stats"]["kernel_launches"]
+
+
+@pytest.mark.parametrize("name", ["dodge_c2", "cube_rot", "plane_diag", "quirks", "soft17_dodge", "glas_nan"])
+@pytest.mark.parametrize("depth", [1, 4])
+def test_camera_kernel_equals_the_separate_launches(rtp, name, depth, monkeypatch):
+    """The camera level runs in one kernel (k_camera: primary rays, their shadow rays, shading and - max_depth 1 - the
+    image; RTP_FUSED=1, the default) or as separate closest / shadow / shade launches (RTP_FUSED=0); read when the scene
+    is created.  Same functions, same arithmetic: every output must agree bit for bit, ray counters included - also
+    with every ray forced through the parked-pixel kernel (k_coop_camera)."""
+    c = load_case(name)
+    m = load_golden_mesh(c["model"])
+    w, h = 3 * int(c["w"]) + 5, 3 * int(c["h"]) + 3  # ragged: tile padding pixels
+    frames = []
+    for fused in ("0", "1"):
+        monkeypatch.setenv("RTP_FUSED", fused)
+        s = make_scene(rtp, m)
+        s.set_lights(c["point_lights"], c["dir_lights"])
+        s.set_camera(w, h, c["view"])
+        frames.append(s.render(w, h, max_depth=depth, want=("rgb", "rgb8", "hit")))
+        s.close()
+    a, b = frames
+    assert np.array_equal(a["hit"], b["hit"]) and bits_equal(a["rgb"], b["rgb"]).all() and np.array_equal(a["rgb8"], b["rgb8"])
+    for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits"):
+        assert a["stats"][k] == b["stats"][k], k
+    assert b["stats"]["kernel_launches"] < a["stats"]["kernel_launches"]
