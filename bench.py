@@ -353,7 +353,7 @@ def run_ours(args, wl, rtp):
 
     t_begin = time.perf_counter()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ms_steps, k_closest, k_any, k_shade, k_cam = [], [], [], [], []
+    ms_steps, k_closest, k_any, k_shade, k_cam, k_paths = [], [], [], [], [], []
     # rays of the camera level alone (k_camera's launch): one untimed frame at max_depth 1 on this rank's tiles
     scene.render_tiles_device(w, h, tg.tiles.data_ptr(), max_depth=1, rank=rank, world=world, stream=stream)
     torch.cuda.synchronize()
@@ -393,6 +393,7 @@ def run_ours(args, wl, rtp):
         k_any.append(fs["ms_anyhit"])
         k_shade.append(fs["ms_shade"])
         k_cam.append(fs["ms_camera"])
+        k_paths.append(fs["ms_paths"])
 
     # end to end through the public C ABI with host buffers (inputs uploaded, image downloaded)
     e2e_ms = []
@@ -456,12 +457,17 @@ def run_ours(args, wl, rtp):
         fusedcam = mcam > 0
         own = (float(st["rays_primary"] + st["rays_reflection"]) - (float(st["rays_primary"]) if fusedcam else 0.0),
                float(st["rays_shadow"]) - ((rays_camera - float(st["rays_primary"])) if fusedcam else 0.0))
-        cands = [("k_camera", mcam, rays_camera if fusedcam else 0.0), ("k_trace<closest>", mc, own[0]), ("k_trace<anyhit>", ms_, own[1])]
+        mpaths = float(np.mean(k_paths))
+        if mpaths > 0:  # levels >= 1 ran in k_paths: the per-level kernels saw the camera level only
+            own = (float(st["rays_primary"]) if not fusedcam else 0.0, (rays_camera - float(st["rays_primary"])) if not fusedcam else 0.0)
+        rays_paths = float(st["rays_primary"] + st["rays_reflection"] + st["rays_shadow"]) - rays_camera if mpaths > 0 else 0.0
+        cands = [("k_camera", mcam, rays_camera if fusedcam else 0.0), ("k_trace<closest>", mc, own[0]), ("k_trace<anyhit>", ms_, own[1]),
+                 ("k_paths", mpaths, rays_paths)]
         dom, dom_ms, dom_rays = max(cands, key=lambda c: c[1])
         roof = roofline_dict(args.workload, dom, dom_ms, dom_rays, n_tris, torch.cuda.get_device_properties(local).multi_processor_count,
                              clocks, peaks,
-                             extra=dict(kernels_ms=dict(camera=mcam, closest=mc, anyhit=ms_, streaming=mo),
-                                        rays_by_kind=dict(camera=rays_camera if fusedcam else 0.0, closest=own[0], anyhit=own[1]),
+                             extra=dict(kernels_ms=dict(camera=mcam, closest=mc, anyhit=ms_, paths=mpaths, streaming=mo),
+                                        rays_by_kind=dict(camera=rays_camera if fusedcam else 0.0, closest=own[0], anyhit=own[1], paths=rays_paths),
                                         kernels_ms_from=f"{args.steps} more steps with RTP_RENDER_PROFILE: per-kernel CUDA events on the launch "
                                                         f"stream, the frame as one tile group (each kernel alone on the GPU, k_coop counted with its "
                                                         f"k_trace, k_coop_camera with k_camera), {float(np.mean(ms_serial)):.4f} ms per step"))

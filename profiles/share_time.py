@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--workload", default="c3")
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--worlds", default="1,2,4,8")
+    ap.add_argument("--all-ranks", action="store_true", help="time every rank's share (default: rank 0 and the last)")
     ap.add_argument("--timeline", action="store_true", help="with RTP_TIMELINE=1: print the launch timeline of the last frames (stderr)")
     a = ap.parse_args()
     wl = bench.build_workload(a.workload, importlib.import_module("ray-tracing-project_b200.synth"))
@@ -37,7 +38,7 @@ def main():
     out = {}
     for world in [int(x) for x in a.worlds.split(",")]:
         per_rank = []
-        for rank in sorted({0, world - 1}):
+        for rank in (range(world) if a.all_ranks else sorted({0, world - 1})):
             ms = []
             for it in range(a.steps + 3):
                 flush.zero_()

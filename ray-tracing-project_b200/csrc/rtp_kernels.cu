@@ -31,6 +31,17 @@ namespace {
 
 constexpr unsigned kFull = 0xffffffffu;
 
+// resident CTAs per SM of the persistent trace kernels (128 threads each): 8 = 64 registers
+#ifndef RTP_TRACE_MINB
+#define RTP_TRACE_MINB 8
+#endif
+#ifndef RTP_RAYS_ANY_MINB
+#define RTP_RAYS_ANY_MINB 9
+#endif
+#ifndef RTP_TRACE_MINB_ANY  // resident CTAs per SM of the any-hit instantiations (experiment builds: 9 = 56 registers)
+#define RTP_TRACE_MINB_ANY RTP_TRACE_MINB
+#endif
+
 // ---- jobs: where a trace kernel gets its rays from and where results go ----------------------
 // CAM = true: level 0 of a camera frame - ray q is pixel q of this rank's tile-major pixel list, generated here.
 // CAM = false: rays come from the level's ray list (reflection levels, caller-supplied rays).
@@ -38,6 +49,7 @@ template <bool CAM>
 struct FrameClosest {
   static constexpr bool kAny = false;
   static constexpr bool kSub = false;
+  static constexpr int kMinBlocks = RTP_TRACE_MINB;
   DeviceScene S;
   // CAM
   DeviceCamera cam;
@@ -128,6 +140,7 @@ template <bool DENSE>
 struct FrameAny {
   static constexpr bool kAny = true;
   static constexpr bool kSub = DENSE;
+  static constexpr int kMinBlocks = RTP_TRACE_MINB_ANY;
   DeviceScene S;
   const float4 *pbuf;
   unsigned char *occl;
@@ -162,6 +175,7 @@ struct FrameAny {
 struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
   static constexpr bool kAny = false;
   static constexpr bool kSub = false;
+  static constexpr int kMinBlocks = RTP_TRACE_MINB;
   DeviceScene S;
   const float *rays;
   int *face;
@@ -187,6 +201,9 @@ struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
 struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
   static constexpr bool kAny = true;
   static constexpr bool kSub = false;
+  // scattered any-hit batches are the one launch that gains from a ninth CTA per SM (56 registers, 16 bytes of spill
+  // outside the node loop): C5 20.40 -> 19.75 ms; the frame kernels lose 1 % (profiles/r02_design_items.md)
+  static constexpr int kMinBlocks = RTP_RAYS_ANY_MINB;
   DeviceScene S;
   const float *rays;
   unsigned char *occ;
@@ -333,9 +350,6 @@ __device__ __forceinline__ void coop_trace(const DeviceScene &S, Trav &t, const 
 }
 
 // ---- the persistent trace kernel -----------------------------------------------------------------
-#ifndef RTP_TRACE_MINB
-#define RTP_TRACE_MINB 8
-#endif
 #ifdef RTP_TRACE_TIMING  // debug builds only (scratch A/B runs): per-warp start / end / last-fetch times
 __device__ unsigned long long g_warp_timing[2 * 8192 * 8];
 __device__ __forceinline__ unsigned long long gtime() {
@@ -345,7 +359,7 @@ __device__ __forceinline__ unsigned long long gtime() {
 }
 #endif
 template <class Job, int kRefillBelow>
-__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_trace(const Job job, const ParkList pl) {
+__global__ void __launch_bounds__(128, Job::kMinBlocks) k_trace(const Job job, const ParkList pl) {
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1u;
   // kSubs (batch mode of a job with sub-batches): the cursor hands out 32 UNITS (pixels) and the warp walks each
@@ -1270,6 +1284,9 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b1, k_trace<FrameAny<true>, 1>, cfg.threads, 0);
   cfg.blocks_closest = sms * (b0 > 0 ? b0 : 1);
   cfg.blocks_any = sms * (b1 > 0 ? b1 : 1);
+  int b4 = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b4, k_trace<RaysAny, 24>, cfg.threads, 0);
+  cfg.blocks_rays_any = sms * (b4 > 0 ? b4 : 1);
   int b2 = 1;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b2, k_paths<24>, 128, 0);
   cfg.blocks_paths = sms * (b2 > 0 ? b2 : 1);
@@ -1349,9 +1366,10 @@ int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st) {
   const bool park_any = park && (g_park_any || p.n_px <= g_any_small);
   // a parked pixel is dear here (k_coop_camera also traces its shadow rays and shades it): above 600 k pixels per launch
   // sequence only the really long rays are parked (C3 1/2 share: 0.441 ms at 6 steps, 0.391 at 14; 1/8 share: 0.172 / 0.235)
-  pk.budget = park ? (g_budget_from_env || p.n_px * cfg.groups <= 600000 ? g_budget : 2 * g_budget) : 0x3fffffff;
+  const int patient = g_budget_from_env || p.n_px * cfg.groups <= 600000 ? 1 : 2;
+  pk.budget = park ? patient * g_budget + (patient - 1) * 2 : 0x3fffffff;  // 6 steps, 14 for the bigger shares
   pk.lanes = g_park_lanes;
-  pk.budget_any = park_any ? g_budget_any : 0x3fffffff;
+  pk.budget_any = park_any ? patient * g_budget_any + (patient - 1) * 2 : 0x3fffffff;
   pk.lanes_any = g_park_lanes_any;
   if (p.max_depth == 1) k_camera<true><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
   else k_camera<false><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
@@ -1409,7 +1427,7 @@ int launch_rays_anyhit(const DeviceScene &S, const float *rays, long long n, uns
                         const LaunchCfg &cfg, cudaStream_t st) {
   RaysAny j;
   j.S = S; j.rays = rays; j.occ = occ; j.cursor = cursor; j.n = (int)n;
-  return launch_trace(j, cfg.blocks_any, cfg, cursor - kCtrAux, 16, false, 1ll << 40, st);  // ray batches: never (C5)
+  return launch_trace(j, cfg.blocks_rays_any, cfg, cursor - kCtrAux, 16, false, 1ll << 40, st);  // ray batches: never (C5)
 }
 
 // ---- ray batches without any allocation (rtp_trace_rays_device_noalloc) ----------------------------------------

@@ -46,7 +46,7 @@ struct FrameParams {
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, blocks_camera = 0, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, blocks_camera = 0, blocks_rays_any = 0, threads = 128;
   int *park_slots = nullptr;  // parked-ray list storage (park_cap * kParkSlotBytes), owned by the scene
   int park_cap = 0;
   int groups = 1;  // tile groups of the frame this launch belongs to (a group's n_px x groups = the rank's pixels)
