@@ -367,7 +367,10 @@ RTP_HD void tile_pixel(int p, int &x, int &y) {
   x = ((sub & 3) << 3) + (lane & 7);
   y = ((sub >> 2) << 2) + (lane >> 3);
 }
-// owner rank of screen tile (tx, ty): diagonal interleave
+// Owner rank of screen tile (tx, ty): diagonal interleave.  A rank's tiles touch at their corners, so neighbouring tiles of
+// a rank share hierarchy nodes in its L2.  (Measured against a hashed rotation of the ranks per run of `world` tiles,
+// profiles/r02_camera.md section 5: the C3 shares at world 8 got slower, 0.171-0.190 -> 0.178-0.204 ms, and the C2 shares
+// no better balanced - their spread is the longest path chain a rank happens to own, not a screen-space pattern.)
 RTP_HD int tile_owner(int tx, int ty, int world) { return (tx + ty) % world; }
 
 }  // namespace rtp

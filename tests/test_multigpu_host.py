@@ -72,9 +72,13 @@ def test_gather_rebuilds_the_frame(world, w, h, tmp_path):
     allb = np.load(out)
     tx, ty = (w + TILE - 1) // TILE, (h + TILE - 1) // TILE
     _, local = rtp.tile_table(w, h, 0, world)
+    owner_of = np.full(tx * ty, -1)
+    for r in range(world):
+        owner_of[rtp.tile_table(w, h, r, world)[0]] = r
+    assert (owner_of >= 0).all()
     seen = np.zeros(w * h, np.int32)
     for t in range(tx * ty):  # the un-tile kernel's addressing, on the host
-        owner = (t % tx + t // tx) % world
+        owner = owner_of[t]
         x0, y0 = (t % tx) * TILE, (t // tx) * TILE
         for y in range(min(TILE, h - y0)):
             xs = np.arange(min(TILE, w - x0))
