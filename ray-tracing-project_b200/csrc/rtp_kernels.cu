@@ -1140,6 +1140,193 @@ __global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, con
   }
 }
 
+// k_paths with HELPERS: parallelism inside a path.  EXPERIMENT, not the default: parity-green (bit-equal to k_paths and to
+// the per-level kernels) and slower on everything measured (C2 levels >= 1: 0.393 -> 0.432 ms, a C4 1/8 share 1.57 -> 1.66,
+// the whole C4 frame through it 5.15 -> 6.45): the claim / report traffic of every scheduling round and the scattered
+// helper rays cost more than the idle lanes were worth, profiles/r02_camera.md section 6.  k_paths walks a hit's shadow rays one after the other in the lane that
+// owns the path - a chain of (1 + lights) traversals per level, of cold node fetches on a big scene - and a small share of
+// a frame (a rank of 8, a small image) is as long as its longest chain while most lanes of the warp sit idle.  Here a lane
+// without a path (the ray list is exhausted, or it is above the refill threshold) takes one of the shadow rays that an
+// owner of its warp has not started yet: the owner publishes the hit (P in shared memory) and hands out light indices
+// through a per-owner counter; whoever traces light li reports the outcome as bit li of the owner's occlusion word; when
+// all lights have reported, the owner adds up calcSingleColor over the unshadowed lights IN LIGHT ORDER (the sum the
+// sequential walk forms, bit for bit) and goes on to the reflection ray.  With every lane busy it degenerates to the
+// sequential walk.  At most 32 lights (one occlusion word); frames with more take the per-level kernels.
+template <int kRefillBelow>
+__global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_paths_help(const FrameParams p, const int first_depth, const int kPathWait,
+                                                                    const int kPathRun) {
+  __shared__ float s_f[PS_SX][128];  // O, D, P, N of the lane's path (no running sum here)
+  __shared__ int s_i[PS_INTS][128];
+  __shared__ int s_next[128], s_done[128];  // per owner: next light to hand out, lights that have reported
+  __shared__ unsigned s_occ[128];           //            bit li: light li is shadowed
+  __shared__ int s_cnt[2 * kMaxDepth];
+  const int tid = threadIdx.x, lane = tid & 31;
+  const unsigned lt = (1u << lane) - 1u;
+  if (tid < 2 * kMaxDepth) s_cnt[tid] = 0;
+  s_next[tid] = 0x40000000;  // no offer
+  __syncthreads();
+#define PF(k) s_f[k][tid]
+#define PI(k) s_i[k][tid]
+  const DeviceScene &S = p.S;
+  const int n_lights = S.n_lights;
+  const int count = p.counters[kCtrPaths + first_depth];
+  int *const cursor = p.counters + kCtrFetchClosest + first_depth;
+  const float4 *ro = p.ray_o[first_depth & 1], *rd = p.ray_d[first_depth & 1];
+  int stack[kStackSize];
+  Trav t;
+  t.node = kSentinel;
+  t.any = false;
+  bool have = false, exhausted = false, helping = false;
+  int h_owner = 0, h_light = 0;  // helping: thread (in the CTA) that owns the path, light this lane traces for it
+  for (;;) {
+    if (helping && t.node == kSentinel) {  // a helper reports as soon as its ray has ended
+      if (t.sbest >= 0) atomicOr(&s_occ[h_owner], 1u << h_light);
+      __threadfence_block();
+      atomicAdd(&s_done[h_owner], 1);
+      helping = false;
+    }
+    __syncwarp();
+    unsigned running = __ballot_sync(kFull, (have || helping) && t.node != kSentinel);
+    const unsigned waiting = __ballot_sync(kFull, have && t.node == kSentinel);
+    if (waiting && (__popc(waiting) >= kPathWait || __popc(running) < kPathRun)) {
+      if (have && t.node == kSentinel) {
+        bool start_light = false, level_ready = false;
+        int li = 0;
+        if (!t.any) {  // a closest-hit traversal has ended
+          if (closest_needs_rerun(S, t, stack)) {
+            // careful re-run from the root: keeps traversing
+          } else if (t.sbest < 0) {
+            have = false;  // the path leaves the scene (flyscene.cpp:327-332)
+          } else {
+            const v3 P = vadd(t.o, vmuls(t.d, t.tbest));  // flyscene.cpp:464
+            const v3 N = interpolate_normal_slot(S, t.sbest, P);
+            PF(PS_PX) = P.x; PF(PS_PY) = P.y; PF(PS_PZ) = P.z;
+            PF(PS_NX) = N.x; PF(PS_NY) = N.y; PF(PS_NZ) = N.z;
+            PI(PS_SLOT) = t.sbest;
+            atomicAdd(&s_cnt[PI(PS_DEPTH)], 1);
+            s_occ[tid] = 0u;
+            s_done[tid] = 0;
+            t.any = true;  // shadow phase (t.node stays at the sentinel until a light is started)
+            if (n_lights > 0) {
+              PI(PS_LIGHT) = 0;  // the owner takes light 0 itself, the others are on offer
+              __threadfence_block();
+              s_next[tid] = 1;
+              start_light = true;
+            } else {
+              PI(PS_LIGHT) = n_lights;
+              level_ready = true;
+            }
+          }
+        } else {  // shadow phase: the owner's own ray has ended, or it only waits for its helpers
+          const int mine = PI(PS_LIGHT);
+          if (mine < n_lights) {
+            if (t.sbest >= 0) atomicOr(&s_occ[tid], 1u << mine);
+            atomicAdd(&s_done[tid], 1);
+            li = atomicAdd(&s_next[tid], 1);
+            if (li < n_lights) start_light = true;
+            else PI(PS_LIGHT) = n_lights;  // every light is with somebody
+          }
+          if (!start_light) level_ready = atomicAdd(&s_done[tid], 0) >= n_lights;
+        }
+        if (start_light) {  // shadow(P, L) for light li (flyscene.cpp:510-526,606-612)
+          const v3 P = mk3(PF(PS_PX), PF(PS_PY), PF(PS_PZ));
+          const v3 L = cam_light_dir(S, li, P);
+          PI(PS_LIGHT) = li;
+          trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);  // flyscene.cpp:512
+          t.any = true;
+        } else if (level_ready) {  // calculateColor in light order, the level's records, the reflection ray
+          s_next[tid] = 0x40000000;
+          const unsigned occ = atomicOr(&s_occ[tid], 0u);
+          const v3 P = mk3(PF(PS_PX), PF(PS_PY), PF(PS_PZ));
+          const v3 N = mk3(PF(PS_NX), PF(PS_NY), PF(PS_NZ));
+          const unsigned mat = (unsigned)f2i(__ldg(S.tris + 4 * (size_t)PI(PS_SLOT) + 2).w) & kTriMatMask;
+          const float4 m0 = __ldg(S.materials + 3 * mat), m1 = __ldg(S.materials + 3 * mat + 1), m2 = __ldg(S.materials + 3 * mat + 2);
+          v3 sum = mk3(0.f, 0.f, 0.f);
+          for (int l = 0; l < n_lights; ++l) {
+            if ((occ >> l) & 1u) continue;  // shadowed (flyscene.cpp:543-545)
+            const float4 l1 = __ldg(S.lights + 2 * l + 1);
+            sum = vadd(sum, phong(xyz(m0), xyz(m1), xyz(m2), m0.w, N, cam_light_dir(S, l, P), xyz(l1),
+                                  mk3(PF(PS_OX), PF(PS_OY), PF(PS_OZ)), P));
+          }
+          const int depth = PI(PS_DEPTH), pixel = PI(PS_PIXEL);
+          RTP_CHECK((unsigned)pixel < (unsigned)p.n_px && (unsigned)depth < (unsigned)p.max_depth, 31, pixel, p.n_px);
+          p.direct[(size_t)depth * p.n_px + pixel] = make_float4(clamp01(sum.x), clamp01(sum.y), clamp01(sum.z), 0.f);
+          p.ksdeep[pixel] = make_float4(m2.x, m2.y, m2.z, i2f(depth + 1));
+          if (depth + 1 < p.max_depth) {
+            const v3 r = reflect_dir(mk3(PF(PS_DX), PF(PS_DY), PF(PS_DZ)), N);  // :361
+            const v3 o2 = vadd(P, vmuls(r, (float)0.001));                       // :362
+            PF(PS_OX) = o2.x; PF(PS_OY) = o2.y; PF(PS_OZ) = o2.z;
+            PF(PS_DX) = r.x; PF(PS_DY) = r.y; PF(PS_DZ) = r.z;
+            PI(PS_DEPTH) = depth + 1;
+            atomicAdd(&s_cnt[kMaxDepth + depth + 1], 1);
+            trav_init(t, o2, r, stack);  // t.any = false: closest hit of the next level
+          } else {
+            have = false;
+          }
+        }
+      }
+    }
+    const unsigned act = __ballot_sync(kFull, have || helping);
+    if (!exhausted && __popc(act) < kRefillBelow) {
+      const unsigned need = ~act;
+      const int n_need = __popc(need);
+      const int leader = __ffs(need) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(cursor, n_need);
+      base = __shfl_sync(kFull, base, leader);
+      exhausted = base + n_need >= count;
+      if (!have && !helping) {
+        const int q = base + __popc(need & lt);
+        if (q < count) {
+          const float4 o4 = ro[q], d4 = rd[q];
+          PF(PS_OX) = o4.x; PF(PS_OY) = o4.y; PF(PS_OZ) = o4.z;
+          PF(PS_DX) = d4.x; PF(PS_DY) = d4.y; PF(PS_DZ) = d4.z;
+          PI(PS_PIXEL) = f2i(o4.w);
+          PI(PS_DEPTH) = first_depth;
+          trav_init(t, xyz(o4), xyz(d4), stack);
+          have = true;
+        }
+      }
+    }
+    __syncwarp();
+    {  // lanes that are still without work take a shadow ray off an owner of this warp
+      const bool idle = !have && !helping;
+      const bool offers = have && t.any && atomicAdd(&s_next[tid], 0) < n_lights;
+      const unsigned idle_m = __ballot_sync(kFull, idle), off_m = __ballot_sync(kFull, offers);
+      if (idle && off_m) {
+        const int ol = __fns(off_m, 0, (__popc(idle_m & lt) % __popc(off_m)) + 1);  // spread the idle lanes over the owners
+        const int otid = (tid & ~31) | ol;
+        const int li = atomicAdd(&s_next[otid], 1);
+        if (li < n_lights) {
+          helping = true;
+          h_owner = otid;
+          h_light = li;
+          const v3 P = mk3(s_f[PS_PX][otid], s_f[PS_PY][otid], s_f[PS_PZ][otid]);
+          const v3 L = cam_light_dir(S, li, P);
+          trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
+          t.any = true;
+        }
+      }
+    }
+    running = __ballot_sync(kFull, (have || helping) && t.node != kSentinel);
+    if (running == 0) {
+      if (__ballot_sync(kFull, have || helping) == 0 && exhausted) break;
+      continue;
+    }
+    if ((have || helping) && t.node != kSentinel)
+      // origin of the reference's BoundingBox test: the un-offset hit point for a shadow ray (the owner's, for a helper),
+      // the ray's own origin for a (careful) closest-hit ray
+      trav_step<2>(S, t, stack, [&] {
+        const int o = helping ? h_owner : tid;
+        return t.any ? mk3(s_f[PS_PX][o], s_f[PS_PY][o], s_f[PS_PZ][o]) : t.o;
+      });
+  }
+#undef PF
+#undef PI
+  __syncthreads();
+  if (tid < 2 * kMaxDepth && s_cnt[tid]) atomicAdd(p.counters + (tid < kMaxDepth ? kCtrHits + tid : kCtrPaths + tid - kMaxDepth), s_cnt[tid]);
+}
+
 __global__ void __launch_bounds__(256) k_untile(const float4 *all, size_t rank_stride_f4, const int *local_of_tile,
                                                 int width, int height, int tiles_x, int world, int only_rank,
                                                 float *rgb, unsigned char *rgb8, int *hit) {
@@ -1386,6 +1573,19 @@ void launch_paths(const FrameParams &p, int first_depth, const LaunchCfg &cfg, c
     refill = e ? std::atoi(e) : 24;
     if ((e = std::getenv("RTP_PATH_WAIT"))) g_path_wait = std::atoi(e);
     if ((e = std::getenv("RTP_PATH_RUN"))) g_path_run = std::atoi(e);
+  }
+  static int help = -1;
+  if (help < 0) {
+    const char *e = std::getenv("RTP_PATH_HELP");
+    help = e ? std::atoi(e) : 0;
+  }
+  // RTP_PATH_HELP=1 (experiment, measured slower - profiles/r02_camera.md section 6): idle lanes trace shadow rays of
+  // their warp's paths
+  if (help && p.S.n_lights <= kCamMaxLights) {
+    if (refill <= 8) k_paths_help<8><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
+    else if (refill <= 24) k_paths_help<24><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
+    else k_paths_help<32><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
+    return;
   }
   if (refill <= 8) k_paths<8><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
   else if (refill <= 24) k_paths<24><<<cfg.blocks_paths, 128, 0, st>>>(p, first_depth, g_path_wait, g_path_run);
