@@ -819,12 +819,19 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   const bool fused = camera_fusable(p) &&
                      (s->fused >= 0 ? s->fused != 0
                                     : (!s->cfg.scene_exceeds_l2 || (long long)p.n_px * std::max(p.S.n_lights, 1) <= s->fused_px));
+  // separate launches at the camera level: the shadow launch carries the level's shading when it does not park rays
+  bool any_shade = !fused;
+  for (int g = 0; g < G && any_shade; ++g) any_shade = anyhit_shade_ok(gp[g], gc[g]);
   for (int d = 0; d < wave_levels; ++d) {
     if (d == 0 && fused) {
       for (int g = 0; g < G; ++g) { CK(mark(4)); n += launch_camera(gp[g], gc[g], gs[g]); CK(stamp("camera", g, d, gs[g])); }
       continue;
     }
     for (int g = 0; g < G; ++g) { CK(mark(0)); n += launch_closest(gp[g], d, gc[g], gs[g]); CK(stamp("closest", g, d, gs[g])); }
+    if (d == 0 && any_shade) {  // the camera level's shadow launch shades its pixels itself
+      for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit_shade(gp[g], gc[g], gs[g]); CK(stamp("anyhit+shade", g, d, gs[g])); }
+      continue;
+    }
     for (int g = 0; g < G; ++g) { CK(mark(1)); n += launch_anyhit(gp[g], d, gc[g], gs[g]); CK(stamp("anyhit", g, d, gs[g])); }
     if (p.max_depth > 1)  // max_depth 1: the resolve kernel shades the only level itself
       for (int g = 0; g < G; ++g) { CK(mark(2)); launch_accum(gp[g], d, gs[g]); ++n; CK(stamp("accum", g, d, gs[g])); }
@@ -832,7 +839,7 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   if (wave_levels < p.max_depth)
     for (int g = 0; g < G; ++g) { CK(mark(3)); launch_paths(gp[g], wave_levels, gc[g], gs[g]); ++n; CK(stamp("paths", g, wave_levels, gs[g])); }
   for (int g = 0; g < G; ++g) {
-    if (!(fused && p.max_depth == 1)) {  // k_camera has written the image of a one-level frame itself
+    if (!((fused || any_shade) && p.max_depth == 1)) {  // k_camera / the shading shadow launch has written a one-level frame's image
       CK(mark(2)); launch_resolve(gp[g], gs[g]); ++n;
       CK(stamp("resolve", g, 0, gs[g]));
     }

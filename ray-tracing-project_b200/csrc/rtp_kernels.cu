@@ -49,6 +49,7 @@ template <bool CAM>
 struct FrameClosest {
   static constexpr bool kAny = false;
   static constexpr bool kSub = false;
+  static constexpr bool kFinish = false;  // no per-unit epilogue in k_trace
   static constexpr int kMinBlocks = RTP_TRACE_MINB;
   DeviceScene S;
   // CAM
@@ -140,6 +141,7 @@ template <bool DENSE>
 struct FrameAny {
   static constexpr bool kAny = true;
   static constexpr bool kSub = DENSE;
+  static constexpr bool kFinish = false;  // no per-unit epilogue in k_trace
   static constexpr int kMinBlocks = RTP_TRACE_MINB_ANY;
   DeviceScene S;
   const float4 *pbuf;
@@ -175,6 +177,7 @@ struct FrameAny {
 struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
   static constexpr bool kAny = false;
   static constexpr bool kSub = false;
+  static constexpr bool kFinish = false;  // no per-unit epilogue in k_trace
   static constexpr int kMinBlocks = RTP_TRACE_MINB;
   DeviceScene S;
   const float *rays;
@@ -201,6 +204,7 @@ struct RaysClosest {  // rtp_trace_rays(CLOSEST): rays n x 6 floats
 struct RaysAny {  // rtp_trace_rays(ANYHIT): shadow(P, L) for rays (P, L)
   static constexpr bool kAny = true;
   static constexpr bool kSub = false;
+  static constexpr bool kFinish = false;  // no per-unit epilogue in k_trace
   // scattered any-hit batches are the one launch that gains from a ninth CTA per SM (56 registers, 16 bytes of spill
   // outside the node loop): C5 20.40 -> 19.75 ms; the frame kernels lose 1 % (profiles/r02_design_items.md)
   static constexpr int kMinBlocks = RTP_RAYS_ANY_MINB;
@@ -383,6 +387,10 @@ __global__ void __launch_bounds__(128, Job::kMinBlocks) k_trace(const Job job, c
   Trav t;
   int q = 0, age = 0;  // age: steps since this warp last took rays (warp-uniform)
   bool have = false, exhausted = false;
+  // Job::kFinish (a job with sub-batches in batch mode): bit s of occ = sub-ray s of this lane's unit found a hit; when the
+  // warp has walked all subs of its 32 units, job.finish(unit, occ) runs the units' epilogue (FrameAnyShade: shading)
+  unsigned occ = 0;
+  bool open = false;  // a batch of units has been taken and not finished yet
   for (;;) {
     // lanes whose traversal is still going (a finished one keeps its result in t until it is retired)
     unsigned act = __ballot_sync(kFull, have && t.node != kSentinel);
@@ -392,15 +400,23 @@ __global__ void __launch_bounds__(128, Job::kMinBlocks) k_trace(const Job job, c
       bool fin = have && t.node == kSentinel;
       if (fin && job.rerun(t, stack)) fin = false;  // careful re-run: node = root again
       job.commit(q, t, fin);                        // all lanes: the warp's hit records are appended together
+      if constexpr (Job::kFinish) {
+        if (fin && t.sbest >= 0) occ |= 1u << (sub - 1);
+      }
       if (fin) have = false;
       act = __ballot_sync(kFull, have);
       if constexpr (kSubs) {
         if (act == 0 && (!exhausted || sub < n_sub)) {
           if (sub >= n_sub) {  // next 32 units
+            if constexpr (Job::kFinish) {
+              if (open) job.finish(ubase + lane, occ);
+              occ = 0;
+            }
             int base = 0;
             if (lane == 0) base = atomicAdd(job.cursor, 32);
             ubase = __shfl_sync(kFull, base, 0);
             exhausted = ubase + 32 >= count;
+            open = ubase < count;
             sub = 0;
           }
           const int u = ubase + lane;
@@ -434,7 +450,12 @@ __global__ void __launch_bounds__(128, Job::kMinBlocks) k_trace(const Job job, c
       }
     }
     if (act == 0) {
-      if (exhausted && sub >= n_sub) break;
+      if (exhausted && sub >= n_sub) {
+        if constexpr (Job::kFinish) {
+          if (open) job.finish(ubase + lane, occ);
+        }
+        break;
+      }
       continue;
     }
     if (++age > pl.budget && __popc(act) <= pl.lanes) {
@@ -948,6 +969,43 @@ __device__ __forceinline__ bool camera_finish(const FrameParams &p, int q, int i
   o2 = vadd(P, vmuls(r, (float)0.001));               // :362
   return true;
 }
+
+// EXPERIMENT (RTP_ANY_SHADE=1, off by default: parity-green, no gain - the tile groups already hide the shading kernel).
+// The camera level's shadow launch with the level's shading folded in (big frames, where the three phases stay separate
+// launches): FrameAny<DENSE> whose warps, once they have walked all lights of their 32 pixels, shade those pixels from
+// the occlusion bits in their registers - k_accum's work at level 0 (max_depth > 1) or the whole of k_resolve_image
+// (max_depth 1: shading, fold, quantisation, image store).  No occl[] round trip, one launch and one tail less per tile
+// group.  Only for launches that do not park shadow rays (a parked ray's outcome arrives after the warp has moved on)
+// and at most 32 lights; otherwise FrameAny + k_accum / k_resolve_image as before.
+template <bool DEPTH1>
+struct FrameAnyShade : FrameAny<true> {
+  static constexpr bool kFinish = true;
+  FrameParams p;
+  __device__ __forceinline__ void commit(int, const Trav &, bool) const {}  // the outcome stays in the lane (k_trace: occ)
+  __device__ __forceinline__ void finish(int q, unsigned occ) const {
+    const int lane = threadIdx.x & 31;
+    int i, j;
+    const bool valid = cam_pixel(p, q, i, j);
+    const bool hit = this->hit_slot[q] >= 0;
+    const float4 pb = hit ? this->pbuf[q] : make_float4(0.f, 0.f, 0.f, i2f(-1));
+    v3 o2 = mk3(0.f, 0.f, 0.f), r = o2;
+    const bool spawn = camera_finish<DEPTH1>(p, q, i, j, valid, hit, xyz(pb), f2i(pb.w), occ, o2, r);
+    if (!DEPTH1) {
+      const unsigned m = __ballot_sync(kFull, spawn);
+      if (m) {
+        const int leader = __ffs(m) - 1;
+        int dst = 0;
+        if (lane == leader) dst = atomicAdd(p.counters + kCtrPaths + 1, __popc(m));
+        dst = __shfl_sync(kFull, dst, leader) + __popc(m & ((1u << lane) - 1u));
+        if (spawn) {
+          RTP_CHECK((unsigned)dst < (unsigned)p.n_px, 30, dst, p.n_px);
+          p.ray_o[1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(q));
+          p.ray_d[1][dst] = make_float4(r.x, r.y, r.z, 1.f);
+        }
+      }
+    }
+  }
+};
 
 template <bool DEPTH1>
 __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_camera(const FrameParams p, const CamPark pk) {
@@ -1535,6 +1593,48 @@ static int launch_anyhit_t(const FrameParams &p, int depth, const LaunchCfg &cfg
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st) {
   if (depth == 0 && !p.user_rays) return launch_anyhit_t<true>(p, depth, cfg, st);  // camera level: dense records
   return launch_anyhit_t<false>(p, depth, cfg, st);
+}
+
+// Would the camera level's shadow launch park rays (launch_trace's policy)?  Then their outcomes arrive in k_coop and the
+// shading cannot ride in the launch.
+bool anyhit_shade_ok(const FrameParams &p, const LaunchCfg &cfg) {
+  read_policy_env();
+  static int on = -1;
+  if (on < 0) {
+    // RTP_ANY_SHADE=1 (experiment, measured level on the device and 3 % slower end to end - profiles/r02_camera.md
+    // section 7): the shadow launch shades; default: k_accum / k_resolve_image after it
+    const char *e = std::getenv("RTP_ANY_SHADE");
+    on = e ? std::atoi(e) : 0;
+  }
+  const bool parks = g_budget > 0 && cfg.park_slots && (g_park_any || p.n_px <= g_any_small) && (cfg.scene_exceeds_l2 || g_park_small);
+  return on && !parks && g_refill < 0 && !p.user_rays && p.tile_ids && p.S.n_lights >= 1 && p.S.n_lights <= kCamMaxLights;
+}
+
+// shadow() for the camera level's (pixel, light) pairs with the level's shading in the same launch (FrameAnyShade)
+int launch_anyhit_shade(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st) {
+  ParkList pl;
+  pl.slots = nullptr; pl.ctr = p.counters + kCtrPark + 2 * 8; pl.cap = 0;
+  pl.budget = 0x3fffffff; pl.lanes = 32; pl.step_nodes = kMaxNodesPerStep;  // never parks
+  auto fill = [&](auto &j) {
+    j.S = p.S;
+    j.pbuf = p.pbuf;
+    j.occl = p.occl;
+    j.cursor = p.counters + kCtrFetchAny;
+    j.hits_ptr = p.counters + kCtrHits;
+    j.hit_slot = p.hit_slot;
+    j.n_px = p.n_px;
+    j.p = p;
+  };
+  if (p.max_depth == 1) {
+    FrameAnyShade<true> j;
+    fill(j);
+    k_trace<FrameAnyShade<true>, 1><<<cfg.blocks_any, cfg.threads, 0, st>>>(j, pl);
+  } else {
+    FrameAnyShade<false> j;
+    fill(j);
+    k_trace<FrameAnyShade<false>, 1><<<cfg.blocks_any, cfg.threads, 0, st>>>(j, pl);
+  }
+  return 1;
 }
 
 bool camera_fusable(const FrameParams &p) {

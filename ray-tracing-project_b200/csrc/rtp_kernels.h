@@ -62,6 +62,10 @@ void launch_raygen(const FrameParams &p, cudaStream_t st);
 int launch_closest(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
 // shadow() for every (hit, light) pair (flyscene.cpp:510-526)
 int launch_anyhit(const FrameParams &p, int depth, const LaunchCfg &cfg, cudaStream_t st);
+// launch_anyhit(0) with the camera level's shading folded in (replaces launch_accum(0) and, at max_depth 1, launch_resolve);
+// anyhit_shade_ok: the frame qualifies (camera rays, 1-32 lights, a launch that does not park shadow rays)
+bool anyhit_shade_ok(const FrameParams &p, const LaunchCfg &cfg);
+int launch_anyhit_shade(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st);
 // The camera level of a frame in one kernel (k_camera: primary rays, their shadow rays, shading, and - max_depth 1 - the
 // image; max_depth > 1: the level-0 records and level 1's ray list), plus k_coop_camera for parked pixels: replaces
 // launch_closest(0) + launch_anyhit(0) + launch_accum(0) and, at max_depth 1, launch_resolve.  camera_fusable: the frame
