@@ -26,6 +26,8 @@ UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us":
 def kind_of(name):
     if "k_camera" in name or "k_coop_camera" in name:
         return "camera"
+    if "k_paths" in name:
+        return "paths"
     if "Closest" in name:
         return "closest"
     if "Any" in name:
@@ -92,7 +94,7 @@ def main():
                  "number), rays = the frame's rays of that kind (bench line).  Written by profiles/make_traffic.py from the "
                  "capture named in `from`; bench.py scales warp_inst and dram_bytes by rays(launch) / rays(entry).")
     ent = T.setdefault(workload, {})
-    knames = {"closest": "k_trace<closest>", "anyhit": "k_trace<anyhit>", "camera": "k_camera"}
+    knames = {"closest": "k_trace<closest>", "anyhit": "k_trace<anyhit>", "camera": "k_camera", "paths": "k_paths"}
     if not cam:
         knames = {"closest": "k_trace<RaysClosest>", "anyhit": "k_trace<RaysAny>"}
     for k, a in acc.items():
