@@ -171,11 +171,6 @@ struct rtp_scene {
   // tile groups of a frame run on their own streams (enqueue_frame): group 0 on the caller's stream
   cudaStream_t gstream[kMaxGroups] = {};
   cudaEvent_t gfork = nullptr, gjoin[kMaxGroups] = {};
-  // the live parked-pixel consumer of a group runs beside the group's k_camera on its own stream (enqueue_frame)
-  cudaStream_t lstream[kMaxGroups] = {};
-  cudaEvent_t lfork[kMaxGroups] = {}, ljoin[kMaxGroups] = {};
-  int live_coop = 0;   // RTP_LIVE_COOP=1 (experiment, measured slower - profiles/r02_camera.md section 8): a live parked-pixel consumer beside k_camera
-  int frame_gen = 0;   // tag of the current frame's parked-pixel records (LaunchCfg::gen)
   // rtp_render_async: two frames may be outstanding; image planes, counters snapshot and events per slot,
   // band copies on their own streams so that the next frame's kernels do not queue behind them
   struct AsyncSlot {
@@ -254,16 +249,6 @@ int init_device_side(rtp_scene *s) {
   for (int i = 1; i < kMaxGroups; ++i) CK(cudaStreamCreateWithFlags(&s->gstream[i], cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&s->gfork, cudaEventDisableTiming));
   for (int i = 1; i < kMaxGroups; ++i) CK(cudaEventCreateWithFlags(&s->gjoin[i], cudaEventDisableTiming));
-  for (int i = 0; i < kMaxGroups; ++i) {
-    {  // pending CTAs of the consumer go first when an SM has room: highest stream priority
-      int lo = 0, hi = 0;
-      CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-      CK(cudaStreamCreateWithPriority(&s->lstream[i], cudaStreamNonBlocking, hi));
-    }
-    CK(cudaEventCreateWithFlags(&s->lfork[i], cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&s->ljoin[i], cudaEventDisableTiming));
-  }
-  if (const char *le = std::getenv("RTP_LIVE_COOP")) s->live_coop = std::atoi(le);
   CK(cudaEventCreateWithFlags(&s->frame_start, cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&s->frame_done, cudaEventDisableTiming));
   if (const char *te = std::getenv("RTP_TIMELINE")) s->timeline = std::atoi(te);
@@ -386,11 +371,6 @@ void destroy_one(rtp_scene *s) {
   for (int i = 1; i < kMaxGroups; ++i) {
     if (s->gstream[i]) { cudaStreamSynchronize(s->gstream[i]); cudaStreamDestroy(s->gstream[i]); }
     if (s->gjoin[i]) cudaEventDestroy(s->gjoin[i]);
-  }
-  for (int i = 0; i < kMaxGroups; ++i) {
-    if (s->lstream[i]) { cudaStreamSynchronize(s->lstream[i]); cudaStreamDestroy(s->lstream[i]); }
-    if (s->lfork[i]) cudaEventDestroy(s->lfork[i]);
-    if (s->ljoin[i]) cudaEventDestroy(s->ljoin[i]);
   }
   if (s->gfork) cudaEventDestroy(s->gfork);
   if (s->frame_start) cudaEventDestroy(s->frame_start);
@@ -799,7 +779,6 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     s->tev_name.push_back(std::string(what) + " g" + std::to_string(g) + " d" + std::to_string(d));
     return cudaEventRecord(s->tev[s->tev_used++], on);
   };
-  s->frame_gen = s->frame_gen % 0x7fffff + 1;
   FrameParams gp[kMaxGroups];
   LaunchCfg gc[kMaxGroups];
   cudaStream_t gs[kMaxGroups];
@@ -808,7 +787,6 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     gc[g] = s->cfg;
     gc[g].park_cap = s->cfg.park_cap / G;
     gc[g].groups = G;
-    gc[g].gen = s->frame_gen;
     gc[g].park_slots = s->cfg.park_slots + (size_t)g * gc[g].park_cap * (kParkSlotBytes / sizeof(int));
     gs[g] = g == 0 ? st : s->gstream[g];
     if (s->l2_persist_mb) { int lrc = apply_l2_window(s, gs[g]); if (lrc) return lrc; }
@@ -844,23 +822,11 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   // separate launches at the camera level: the shadow launch carries the level's shading when it does not park rays
   bool any_shade = !fused;
   for (int g = 0; g < G && any_shade; ++g) any_shade = anyhit_shade_ok(gp[g], gc[g]);
-  // RTP_LIVE_COOP=1: k_coop_camera's chain of dependent fetches (50-70 us on a small share) runs beside k_camera instead of
-  // behind it.  Parity-green and slower: every resident consumer CTA costs k_camera a CTA slot of the SM it sits on.
-  const bool live = fused && s->live_coop && !profile && camera_parks(gc[0]);
   for (int d = 0; d < wave_levels; ++d) {
     if (d == 0 && fused) {
       for (int g = 0; g < G; ++g) {
         CK(mark(4));
-        if (live) {
-          // the parked-pixel consumer beside k_camera: fork a second stream, join it, then the sweeping pass
-          CK(cudaEventRecord(s->lfork[g], gs[g]));
-          CK(cudaStreamWaitEvent(s->lstream[g], s->lfork[g], 0));
-          n += launch_camera(gp[g], gc[g], gs[g], 1); CK(stamp("camera", g, d, gs[g]));
-          n += launch_camera(gp[g], gc[g], s->lstream[g], 3); CK(stamp("camera coop live", g, d, s->lstream[g]));
-          CK(cudaEventRecord(s->ljoin[g], s->lstream[g]));
-          CK(cudaStreamWaitEvent(gs[g], s->ljoin[g], 0));
-          n += launch_camera(gp[g], gc[g], gs[g], 2); CK(stamp("camera sweep", g, d, gs[g]));
-        } else if (s->timeline && !profile) {  // RTP_TIMELINE: where the parked-pixel kernel starts
+        if (s->timeline && !profile) {  // RTP_TIMELINE: where the parked-pixel kernel starts
           n += launch_camera(gp[g], gc[g], gs[g], 1); CK(stamp("camera", g, d, gs[g]));
           n += launch_camera(gp[g], gc[g], gs[g], 2); CK(stamp("camera coop", g, d, gs[g]));
         } else {

@@ -890,13 +890,10 @@ constexpr int kCamAnyFlag = 1 << 29;
 constexpr int kCamMaxLights = 32;         // occlusion bits of a pixel live in one register
 constexpr int kCamMaxPixels = 1 << 24;    // pixel id field of a parked record
 struct CamPark {
-  int *slots, *ctr;  // ctr[0] records parked, ctr[1] tickets handed out by the live consumer (k_coop_camera<LIVE>)
-  int *live;         // live[0] warps of k_camera that have left, live[1] cursor of the sweeping pass
+  int *slots, *ctr;
   int cap;
   int budget, lanes;          // primary rays: steps a warp spends on a batch before the rays still running are parked
   int budget_any, lanes_any;  // shadow rays
-  int gen;                    // this launch's tag in a record's word [4] (n | gen << 8): written LAST, it publishes the record
-  int producer_warps;         // warps of the k_camera launch (the live consumer stops when all have left)
 };
 
 // pixel q of this rank's tile-major pixel list -> image coordinates; false: tile padding outside the image
@@ -926,10 +923,8 @@ __device__ __forceinline__ bool cam_park(const CamPark &pk, int head, int a1, in
   for (int i = 1; i <= t.sp; ++i) e[5 + n++] = RTP_STK(stack, i);
   if (t.node != kSentinel) e[5 + n++] = t.node;
   RTP_CHECK(5 + n <= kParkInts - 2, 25, 5 + n, kParkInts - 2);
+  e[4] = n;
   e[kParkInts - 2] = x0; e[kParkInts - 1] = x1;
-  // publish: a consumer that runs beside this kernel (k_coop_camera<LIVE>) polls word [4] for this launch's tag
-  __threadfence();
-  *(volatile int *)(e + 4) = n | (pk.gen << 8);
   return true;
 }
 
@@ -1120,67 +1115,32 @@ __global__ void __launch_bounds__(128, RTP_TRACE_MINB) k_camera(const FrameParam
       }
     }
   }
-  __threadfence();  // this warp's parked records are published before it is counted out
-  if (lane == 0) atomicAdd(pk.live, 1);
 }
 
 // Finishes the pixels k_camera parked, one warp per pixel.
-// LIVE = true: launched BESIDE k_camera on a second stream (small shares: the parked-pixel pass is a chain of dependent
-// fetches per pixel, 50-70 us that would otherwise follow the camera kernel).  A warp takes a ticket k and waits until record
-// k is published (word [4] carries this launch's tag) or every warp of k_camera has left without producing it; it stops
-// taking tickets once the producers are done - what is left then goes to the sweeping pass, which has more warps.  Waits are
-// bounded (no hang if the producers never get to run): a record a live warp gave up on is simply swept.
-// LIVE = false: the sweeping pass behind both kernels - every published record of this launch that nobody has finished
-// (all of them when there is no live consumer).  A finished record's word [4] is cleared.
-template <bool DEPTH1, bool LIVE>
+template <bool DEPTH1>
 __global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, const CamPark pk) {
   __shared__ int s_ws[4][kCoopStack];
   int *const ws = s_ws[threadIdx.x >> 5];
   const int lane = threadIdx.x & 31;
   const DeviceScene &S = p.S;
   const int n_lights = S.n_lights;
-  const int n_parked = LIVE ? pk.cap : min(*pk.ctr, pk.cap);
+  const int n_parked = min(*pk.ctr, pk.cap);
   int stack[1];  // trav_init / closest_needs_rerun write stack[0] only
   for (;;) {
     int k = 0;
-    if (lane == 0) k = atomicAdd(LIVE ? pk.ctr + 1 : pk.live + 1, 1);
+    if (lane == 0) k = atomicAdd(pk.ctr + 1, 1);
     k = __shfl_sync(kFull, k, 0);
     if (k >= n_parked) break;
-    int *e = pk.slots + (size_t)k * kParkInts;
-    int tag = 0;
-    if (LIVE) {
-      if (lane == 0) {
-        unsigned long long t0, t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        for (;;) {
-          tag = *(volatile int *)(e + 4);
-          if ((tag >> 8) == pk.gen) break;
-          if (*(volatile int *)pk.live >= pk.producer_warps) {  // the producers have left: one last look
-            tag = *(volatile int *)(e + 4);
-            break;
-          }
-          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-          if (t1 - t0 > 20000000ull) break;  // 20 ms: give up, the sweeping pass takes it
-          __nanosleep(256);
-        }
-      }
-      tag = __shfl_sync(kFull, tag, 0);
-      if ((tag >> 8) != pk.gen) break;  // no such record (any more): this warp is done
-      __threadfence();
-    } else {
-      tag = e[4];
-      if ((tag >> 8) != pk.gen) continue;  // finished by the live consumer
-    }
-    const int head = LIVE ? __ldcg(e) : e[0];
+    const int *e = pk.slots + (size_t)k * kParkInts;
+    const int head = e[0];
     const int q = (head & (kCamMaxPixels - 1)) - 1;
     RTP_CHECK((unsigned)q < (unsigned)p.n_px, 26, q, p.n_px);
     int i, j;
     cam_pixel(p, q, i, j);  // a parked pixel is inside the image
-    int n = tag & 0xff;
+    int n = e[4];
     RTP_CHECK(n >= 0 && 5 + n <= kParkInts - 2, 24, n, kParkInts - 7);
-    for (int x = lane; x < n; x += 32) ws[x] = LIVE ? __ldcg(e + 5 + x) : e[5 + x];
-    const int e1 = LIVE ? __ldcg(e + 1) : e[1], e2 = LIVE ? __ldcg(e + 2) : e[2], e3 = LIVE ? __ldcg(e + 3) : e[3];
-    const int ex0 = LIVE ? __ldcg(e + kParkInts - 2) : e[kParkInts - 2], ex1 = LIVE ? __ldcg(e + kParkInts - 1) : e[kParkInts - 1];
+    for (int x = lane; x < n; x += 32) ws[x] = e[5 + x];
     __syncwarp();
     Trav t;
     v3 P = mk3(0.f, 0.f, 0.f);
@@ -1189,7 +1149,7 @@ __global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, con
     bool hit;
     if (!(head & kCamAnyFlag)) {  // the pixel's primary ray: the same ray in every lane
       trav_init(t, mk3(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]), primary_dir(p.cam, i, j), stack);
-      t.tbest = i2f(e1); t.rbest = (unsigned)e2; t.sbest = e3; t.careful = head < 0;
+      t.tbest = i2f(e[1]); t.rbest = (unsigned)e[2]; t.sbest = e[3]; t.careful = head < 0;
       for (;;) {
         coop_trace<false>(S, t, t.o, ws, n);
         if (!closest_needs_rerun(S, t, stack)) break;
@@ -1205,9 +1165,9 @@ __global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, con
       }
     } else {  // its shadow ray towards light li: hit point, slot and the bits of the lights before it come with the record
       hit = true;
-      P = mk3(i2f(e1), i2f(e2), i2f(e3));
-      slot = ex0;
-      occ = (unsigned)ex1;
+      P = mk3(i2f(e[1]), i2f(e[2]), i2f(e[3]));
+      slot = e[kParkInts - 2];
+      occ = (unsigned)e[kParkInts - 1];
       li = (head >> 24) & (kCamMaxLights - 1);
       const v3 L = cam_light_dir(S, li, P);
       trav_init(t, vadd(P, vmuls(L, (float)0.003)), L, stack);
@@ -1233,12 +1193,6 @@ __global__ void __launch_bounds__(128, 4) k_coop_camera(const FrameParams p, con
         p.ray_o[1][dst] = make_float4(o2.x, o2.y, o2.z, i2f(q));
         p.ray_d[1][dst] = make_float4(r.x, r.y, r.z, 1.f);
       }
-      *(volatile int *)(e + 4) = 0;  // finished
-    }
-    if (LIVE) {  // the producers are done: leave the rest to the sweeping pass and its wider grid
-      int gone = 0;
-      if (lane == 0) gone = *(volatile int *)pk.live >= pk.producer_warps;
-      if (__shfl_sync(kFull, gone, 0)) break;
     }
     __syncwarp();
   }
@@ -1585,13 +1539,6 @@ void query_launch_cfg(int device, LaunchCfg &cfg) {
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b3, k_camera<true>, 128, 0);
   cfg.blocks_camera = sms * (b3 > 0 ? b3 : 1);
   cfg.blocks_coop = sms * 2;
-  // the live parked-pixel consumer is small on purpose: its warps mostly wait, and every resident CTA of it takes registers
-  // from k_camera (148 CTAs x 128 threads per tile group cost the camera kernels half their warps: 0.19 -> 0.27 ms on a
-  // 1/8 share of C3).  RTP_LIVE_BLOCKS (CTAs, default one per SM) x RTP_LIVE_THREADS (default 32: one warp per CTA)
-  cfg.blocks_coop_live = sms;
-  cfg.live_threads = 32;
-  if (const char *e = std::getenv("RTP_LIVE_BLOCKS")) cfg.blocks_coop_live = std::max(1, std::atoi(e));
-  if (const char *e = std::getenv("RTP_LIVE_THREADS")) cfg.live_threads = std::min(128, std::max(32, std::atoi(e) / 32 * 32));
   if (const char *e = std::getenv("RTP_COOP_BLOCKS")) cfg.blocks_coop = sms * std::max(1, std::atoi(e));  // per SM (tuning runs)
 }
 
@@ -1690,12 +1637,6 @@ int launch_anyhit_shade(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t
   return 1;
 }
 
-// does launch_camera park pixels (then k_coop_camera runs, and its live form may run beside k_camera)?
-bool camera_parks(const LaunchCfg &cfg) {
-  read_policy_env();
-  return g_budget > 0 && cfg.park_slots && (cfg.scene_exceeds_l2 || g_park_small);
-}
-
 bool camera_fusable(const FrameParams &p) {
   return !p.user_rays && p.tile_ids && p.S.n_lights <= kCamMaxLights && p.n_px < kCamMaxPixels;
 }
@@ -1704,14 +1645,8 @@ int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st, i
   read_policy_env();
   CamPark pk;
   pk.slots = cfg.park_slots;
-  pk.ctr = p.counters + kCtrPark;           // launch slot 0
-  pk.live = p.counters + kCtrPark + 2 * 8;  // launch slot 8 (the camera level's shadow launch: unused beside k_camera)
+  pk.ctr = p.counters + kCtrPark;  // launch slot 0
   pk.cap = cfg.park_cap;
-  pk.gen = cfg.gen;
-  // no more CTAs than there are batches for their warps: on a small share the rest of the SMs is free from the first
-  // microsecond for the other tile groups' kernels and for the live parked-pixel consumer
-  const int blocks_cam = std::max(1, std::min(cfg.blocks_camera, (p.n_px / 32 + 3) / 4));
-  pk.producer_warps = blocks_cam * 4;
   // the straggler policy of launch_trace: closest-hit rays park on scenes that spill out of the L2, shadow rays only
   // when the launch is small as well
   const bool park = g_budget > 0 && cfg.park_slots && (cfg.scene_exceeds_l2 || g_park_small);
@@ -1725,19 +1660,13 @@ int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st, i
   pk.lanes_any = g_park_lanes_any;
   int n = 0;
   if (phase == 0 || phase == 1) {
-    if (p.max_depth == 1) k_camera<true><<<blocks_cam, 128, 0, st>>>(p, pk);
-    else k_camera<false><<<blocks_cam, 128, 0, st>>>(p, pk);
+    if (p.max_depth == 1) k_camera<true><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
+    else k_camera<false><<<cfg.blocks_camera, 128, 0, st>>>(p, pk);
     ++n;
   }
-  if (park && phase == 3) {  // the live consumer: one CTA per SM, so that the consumers of all tile groups together can
-                             // never keep k_camera's CTAs off an SM
-    if (p.max_depth == 1) k_coop_camera<true, true><<<cfg.blocks_coop_live, cfg.live_threads, 0, st>>>(p, pk);
-    else k_coop_camera<false, true><<<cfg.blocks_coop_live, cfg.live_threads, 0, st>>>(p, pk);
-    return 1;
-  }
   if (park && (phase == 0 || phase == 2)) {
-    if (p.max_depth == 1) k_coop_camera<true, false><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
-    else k_coop_camera<false, false><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
+    if (p.max_depth == 1) k_coop_camera<true><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
+    else k_coop_camera<false><<<cfg.blocks_coop, 128, 0, st>>>(p, pk);
     ++n;
   }
   return n;

@@ -46,10 +46,9 @@ struct FrameParams {
 };
 
 struct LaunchCfg {
-  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, blocks_camera = 0, blocks_rays_any = 0, blocks_coop_live = 0, live_threads = 32, threads = 128;
+  int blocks_closest = 0, blocks_any = 0, blocks_coop = 0, blocks_paths = 0, blocks_camera = 0, blocks_rays_any = 0, threads = 128;
   int *park_slots = nullptr;  // parked-ray list storage (park_cap * kParkSlotBytes), owned by the scene
   int park_cap = 0;
-  int gen = 1;     // tag of this frame's parked-pixel records (1 .. 2^23: a record's word [4] is n | gen << 8)
   int groups = 1;  // tile groups of the frame this launch belongs to (a group's n_px x groups = the rank's pixels)
   bool scene_exceeds_l2 = false;  // nodes + triangles larger than half the L2: traversal chains run on cold lines
 };
@@ -72,9 +71,7 @@ int launch_anyhit_shade(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t
 // launch_closest(0) + launch_anyhit(0) + launch_accum(0) and, at max_depth 1, launch_resolve.  camera_fusable: the frame
 // qualifies (camera rays, at most 32 lights, fewer than 2^24 pixels per launch).  Returns the kernels launched.
 bool camera_fusable(const FrameParams &p);
-// phase 0: k_camera + the sweeping k_coop_camera, 1: k_camera only, 2: the sweeping pass only, 3: the LIVE k_coop_camera
-// (to be launched on a second stream beside phase 1; phase 2 then follows both)
-bool camera_parks(const LaunchCfg &cfg);
+// phase 0: both kernels, 1: k_camera only, 2: k_coop_camera only (launch timelines stamp between the two)
 int launch_camera(const FrameParams &p, const LaunchCfg &cfg, cudaStream_t st, int phase = 0);
 // every bounce level from first_depth on, path by path, in one persistent kernel (k_paths): replaces the per-level
 // launch_closest / launch_anyhit / launch_accum sequence below the camera level
