@@ -319,3 +319,26 @@ def test_camera_kernel_equals_the_separate_launches(rtp, name, depth, monkeypatc
     for k in ("rays_primary", "rays_shadow", "rays_reflection", "hits"):
         assert a["stats"][k] == b["stats"][k], k
     assert b["stats"]["kernel_launches"] < a["stats"]["kernel_launches"]
+
+
+@pytest.mark.parametrize("fused", ["0", "1"])
+@pytest.mark.parametrize("depth", [1, 3])
+def test_frame_without_lights_and_with_directional_lights_only(rtp, po, fused, depth, monkeypatch):
+    """Edge cases of the light loop on both camera-level paths: no light at all (every hit shades to black, reflections
+    still bounce: flyscene.cpp:603-614 sums nothing), and directional lights only (flyscene.cpp:611)."""
+    monkeypatch.setenv("RTP_FUSED", fused)
+    c = load_case("cube_dirlight")
+    m = load_golden_mesh(c["model"])
+    w, h = 2 * int(c["w"]) + 7, 2 * int(c["h"]) + 1
+    none = np.zeros((0, 6), np.float32)  # (None would mean the reference's default light)
+    for point, dirl in ((none, none), (none, c["dir_lights"])):
+        s = make_scene(rtp, m)
+        s.set_lights(point, dirl)
+        s.set_camera(w, h, c["view"])
+        out = s.render(w, h, max_depth=depth)
+        s.close()
+        o = po.render(m, w, h, view=c["view"], max_depth=depth, point_lights=point, dir_lights=dirl, threads=4)
+        check_image(out["rgb"].reshape(-1, 3), out["hit"].ravel(), o["rgb"], o["hit"])
+        assert out["stats"]["rays_shadow"] == o["counts"]["shadow"] and out["stats"]["rays_reflection"] == o["counts"]["reflection"]
+        if len(dirl) == 0:
+            assert out["stats"]["rays_shadow"] == 0 and out["stats"]["hits"] > 0
