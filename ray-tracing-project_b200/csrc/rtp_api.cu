@@ -194,6 +194,7 @@ struct rtp_scene {
   int fused_px = 1300000;  // RTP_FUSED_PX: scenes that spill out of the L2 fuse up to this many pixel x light pairs per rank
   int l2_persist_mb = 0;
   std::vector<cudaStream_t> l2_streams;  // streams that carry the window already
+  int stagger = 0;      // RTP_STAGGER=1: every tile group on its own prioritised stream (band 0 first)
   int groups = 0;       // rtp_set_tile_groups / RTP_GROUPS; 0 = automatic (auto_groups)
   int last_groups = 1;  // groups of the most recently enqueued frame (their counters are summed)
   std::vector<cudaEvent_t> kev;  // per-kernel events (RTP_RENDER_PROFILE)
@@ -246,7 +247,17 @@ namespace {
 int init_device_side(rtp_scene *s) {
   CK(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
   for (auto &ev : s->ev) CK(cudaEventCreate(&ev));
-  for (int i = 1; i < kMaxGroups; ++i) CK(cudaStreamCreateWithFlags(&s->gstream[i], cudaStreamNonBlocking));
+  {
+    // Group g's stream has priority greatest + g (group 0 highest): when an SM has room, the pending CTAs of an earlier
+    // band go first, so band 0 is through its three kernels while the later bands still trace and its rows are on
+    // their way to the host under their kernels (RTP_STAGGER, enqueue_frame)
+    int least = 0, greatest = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+    if (const char *se = std::getenv("RTP_STAGGER")) s->stagger = std::atoi(se);
+    for (int i = s->stagger ? 0 : 1; i < kMaxGroups; ++i)
+      CK(cudaStreamCreateWithPriority(&s->gstream[i], cudaStreamNonBlocking, s->stagger ? std::min(least, greatest + i) : least));
+    if (s->stagger) CK(cudaEventCreateWithFlags(&s->gjoin[0], cudaEventDisableTiming));
+  }
   CK(cudaEventCreateWithFlags(&s->gfork, cudaEventDisableTiming));
   for (int i = 1; i < kMaxGroups; ++i) CK(cudaEventCreateWithFlags(&s->gjoin[i], cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&s->frame_start, cudaEventDisableTiming));
@@ -368,7 +379,7 @@ void destroy_one(rtp_scene *s) {
     if (ev) cudaEventDestroy(ev);
   for (auto &ev : s->kev) cudaEventDestroy(ev);
   for (auto &ev : s->tev) cudaEventDestroy(ev);
-  for (int i = 1; i < kMaxGroups; ++i) {
+  for (int i = 0; i < kMaxGroups; ++i) {
     if (s->gstream[i]) { cudaStreamSynchronize(s->gstream[i]); cudaStreamDestroy(s->gstream[i]); }
     if (s->gjoin[i]) cudaEventDestroy(s->gjoin[i]);
   }
@@ -788,13 +799,13 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
     gc[g].park_cap = s->cfg.park_cap / G;
     gc[g].groups = G;
     gc[g].park_slots = s->cfg.park_slots + (size_t)g * gc[g].park_cap * (kParkSlotBytes / sizeof(int));
-    gs[g] = g == 0 ? st : s->gstream[g];
+    gs[g] = g == 0 && !(s->stagger && G > 1 && !profile) ? st : s->gstream[g];
     if (s->l2_persist_mb) { int lrc = apply_l2_window(s, gs[g]); if (lrc) return lrc; }
   }
   const bool fork = G > 1 && !profile;
   if (fork) {
     CK(cudaEventRecord(s->gfork, st));
-    for (int g = 1; g < G; ++g) CK(cudaStreamWaitEvent(gs[g], s->gfork, 0));
+    for (int g = s->stagger ? 0 : 1; g < G; ++g) CK(cudaStreamWaitEvent(gs[g], s->gfork, 0));
   }
   CK(stamp("start", 0, 0, st));
   // launches are issued phase by phase across the groups, so that the groups advance together
@@ -856,7 +867,7 @@ int enqueue_frame(rtp_scene *s, const FrameParams &p, cudaStream_t st, int *laun
   CK(mark(-1));
   CK(cudaGetLastError());
   if (fork)
-    for (int g = 1; g < G; ++g) {
+    for (int g = s->stagger ? 0 : 1; g < G; ++g) {
       CK(cudaEventRecord(s->gjoin[g], gs[g]));
       CK(cudaStreamWaitEvent(st, s->gjoin[g], 0));
     }
